@@ -1,0 +1,184 @@
+/*
+ * tdk.h -- C-ABI of libtdk_b200.so: Tadataka's semi-dense inverse-depth path on B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Each entry point replaces one function of the reference's
+ * pyo3 extension `rust_bindings` (the FFI the reference's Python calls); the citation beside
+ * each declaration is the reference interface it stands in for (paths relative to the
+ * reference checkout).  Plain pointers and sizes only, no torch / numpy types.
+ *
+ * Conventions
+ *   - every entry point returns 0 (TDK_OK) or a negative TDK_ERR_* code; tdk_last_error()
+ *     gives the message of the calling thread's last failure;
+ *   - `*_dev` entry points take DEVICE pointers, enqueue on `stream` (a cudaStream_t passed as
+ *     void*; NULL = legacy default stream) and do not synchronise unless stated;
+ *   - `*_host` entry points take HOST pointers, stage through a grow-only per-process device
+ *     arena, and return after the results are back in host memory;
+ *   - images and maps are row-major [H,W]; coordinates are (x, y); a camera is 4 doubles
+ *     {fx, fy, ox, oy}; a transform is a row-major 4x4 (16 doubles);
+ *   - params is 6 HOST doubles {min_depth, max_depth, geo_coeff, photo_coeff, ref_step_size,
+ *     min_gradient}: the arguments of rust_bindings.semi_dense.Params in order
+ *     (src/py/semi_dense.rs:91-109); the inversion of the depth range happens inside;
+ *   - all arithmetic is IEEE f64 without FMA contraction, evaluated in the reference's order.
+ */
+#ifndef TDK_H_
+#define TDK_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    TDK_OK = 0,
+    TDK_ERR_INVALID = -1,     /* bad argument (null pointer, non-positive size, bad step)       */
+    TDK_ERR_CUDA = -2,        /* a CUDA runtime call failed; see tdk_last_error()               */
+    TDK_ERR_AGE = -3,         /* an age exceeds the number of reference frames
+                                 (the reference prints and exits: semi_dense.rs:202-205)        */
+    TDK_ERR_SINGULAR = -4,    /* a reference pose is not invertible (the reference panics in
+                                 transform_wr.inv().unwrap(), semi_dense.rs:87)                 */
+    TDK_ERR_WORKSPACE = -5,   /* workspace too small                                            */
+    TDK_ERR_SEARCH_LEN = -6,  /* an epipolar search line exceeds TDK_MAX_SEARCH_SAMPLES         */
+    TDK_ERR_RANGE = -7        /* coordinate outside the image (tadataka/interpolation/
+                                 __init__.py:23-29 raises ValueError)                           */
+};
+
+/* src/semi_dense/flag.rs:3-14 == tadataka/vo/semi_dense/flag.py:4-14 */
+enum {
+    TDK_FLAG_SUCCESS = 0,
+    TDK_FLAG_HYPOTHESIS_OUT_OF_SEARCH_RANGE = -1,
+    TDK_FLAG_KEY_OUT_OF_RANGE = -2,
+    TDK_FLAG_REF_CLOSE_OUT_OF_RANGE = -3,
+    TDK_FLAG_REF_FAR_OUT_OF_RANGE = -4,
+    TDK_FLAG_REF_EPIPOLAR_TOO_SHORT = -5,
+    TDK_FLAG_INSUFFICIENT_GRADIENT = -6,
+    TDK_FLAG_NEGATIVE_PRIOR_DEPTH = -7,
+    TDK_FLAG_NEGATIVE_REF_DEPTH = -8,
+    TDK_FLAG_NOT_PROCESSED = -9
+};
+
+#define TDK_MAX_SEARCH_SAMPLES (1 << 20)
+
+const char *tdk_last_error(void);
+/* "tadataka-b200 <version> sm_100a" */
+const char *tdk_version(void);
+
+/* ------------------------------------------------------------------ update_depth
+ * Replaces rust_bindings.semi_dense.update_depth (src/py/semi_dense.rs:157-187 ->
+ * src/semi_dense/semi_dense.rs:160-234), batched over P independent keyframes, each with its own
+ * R reference frames; pixel (y,x) of keyframe p uses reference R - age[p,y,x] (semi_dense.rs:207).
+ *
+ *   key_imgs [P,H,W]  key_cams [P,4]  T_wk [P,16]
+ *   ref_imgs [P,R,H,W]  ref_cams [P,R,4]  T_wr [P,R,16]
+ *   age [P,H,W] u64   prior_depth, prior_variance [P,H,W]
+ *   out_depth, out_variance [P,H,W] f64   out_flag [P,H,W] i64
+ *   dbg_argmin (optional) [P,H,W] i32: search result argmin+2 (intensities.rs:32-36), -1 where no
+ *       search ran -- the "extra debug output" the parity gate compares
+ *   out_hist (optional) [P,10] u64: per-keyframe count of each flag, index = -flag; ADDED to
+ *   workspace: tdk_update_depth_workspace_bytes(P,R) bytes of device scratch
+ *
+ * tdk_update_depth_status() copies the launch's status word back (synchronises the stream) and
+ * returns TDK_OK / TDK_ERR_AGE / TDK_ERR_SINGULAR / TDK_ERR_SEARCH_LEN.
+ */
+size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R);
+
+int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const double *T_wk,
+                         const double *ref_imgs, const double *ref_cams, const double *T_wr,
+                         const uint64_t *age, const double *prior_depth,
+                         const double *prior_variance, const double *params, int64_t P, int64_t R,
+                         int64_t H, int64_t W, double *out_depth, double *out_variance,
+                         int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
+                         void *workspace, size_t workspace_bytes, void *stream);
+
+/* Same, for frames that live in separate allocations (a keyframe ring kept on the device):
+ * key_img_ptrs [P] and ref_img_ptrs [P*R] are HOST arrays of DEVICE image pointers. */
+int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double *key_cams,
+                                const double *T_wk, const double *const *ref_img_ptrs,
+                                const double *ref_cams, const double *T_wr, const uint64_t *age,
+                                const double *prior_depth, const double *prior_variance,
+                                const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
+                                double *out_depth, double *out_variance, int64_t *out_flag,
+                                int32_t *dbg_argmin, uint64_t *out_hist, void *workspace,
+                                size_t workspace_bytes, void *stream);
+
+int tdk_update_depth_status(const void *workspace, void *stream);
+
+/* Tuning knob with no counterpart in the reference: how many lanes (8, 16 or 32) cooperate on
+ * one pixel's epipolar search.  Results do not depend on it.  Default 16. */
+int tdk_set_search_lanes(int lanes);
+
+/* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,
+ * checks the status.  Host buffers may be pageable or pinned. */
+int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const double *T_wk,
+                          const double *ref_imgs, const double *ref_cams, const double *T_wr,
+                          const uint64_t *age, const double *prior_depth,
+                          const double *prior_variance, const double *params, int64_t P, int64_t R,
+                          int64_t H, int64_t W, double *out_depth, double *out_variance,
+                          int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist);
+
+/* Replaces rust_bindings.semi_dense.estimate_debug_ (src/py/semi_dense.rs:126-155): one pixel,
+ * host pointers, returns the prior on failure.  u_key is (x, y).  out = {depth, variance},
+ * *out_flag the flag, dbg (optional, 1 value) = argmin+2 of the search, or -1. */
+int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double prior_variance,
+                            const double *key_img, const double *key_cam, const double *T_wk,
+                            const double *ref_img, const double *ref_cam, const double *T_wr,
+                            const double *params, int64_t H, int64_t W, double *out,
+                            int64_t *out_flag, int64_t *dbg);
+
+/* ------------------------------------------------------------------ companions
+ * tdk_fusion_dev: src/semi_dense/fusion.rs:13-42 (`fusion_arrays`; not exported by the reference's
+ * pyo3 module, called as tadataka.vo.semi_dense.fusion.fusion in examples/semi_dense_depth.py:41).
+ * If flag != NULL only elements with flag == 0 are fused, the others keep (mu1, var1): the
+ * "fuse where the update succeeded" step of examples/semi_dense_vo.py:82-88. */
+int tdk_fusion_dev(const double *mu1, const double *mu2, const double *var1, const double *var2,
+                   const int64_t *flag, int64_t n, double *mu, double *var, void *stream);
+
+/* src/semi_dense/regularization.rs:29-64 (disabled in the reference build; semantics as written):
+ * per keyframe [P,H,W]. */
+int tdk_regularize_dev(const double *depth, const double *variance, const int64_t *flag, int64_t P,
+                       int64_t H, int64_t W, double *out_depth, void *stream);
+
+/* rust_bindings.semi_dense.increment_age (src/py/semi_dense.rs:35-51 -> src/semi_dense/age.rs:6-32)
+ * for P independent frames: age0 [P,H,W] u64, cam0/cam1 [P,4], T10 [P,16], depth0 [P,H,W].
+ * workspace: tdk_increment_age_workspace_bytes(P,H,W). */
+size_t tdk_increment_age_workspace_bytes(int64_t P, int64_t H, int64_t W);
+int tdk_increment_age_dev(const uint64_t *age0, const double *cam0, const double *cam1,
+                          const double *T10, const double *depth0, int64_t P, int64_t H, int64_t W,
+                          uint64_t *age1, void *workspace, size_t workspace_bytes, void *stream);
+
+/* rust_bindings.semi_dense.propagate (src/py/semi_dense.rs:189-218 ->
+ * src/semi_dense/propagation.rs:48-92) for P independent frames.  Collisions are folded in raster
+ * order of the source pixel, as the reference's loop does.
+ * workspace: tdk_propagate_workspace_bytes(P,H,W). */
+size_t tdk_propagate_workspace_bytes(int64_t P, int64_t H, int64_t W);
+int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1,
+                      const double *depth0, const double *variance0, int64_t P, int64_t H,
+                      int64_t W, double default_depth, double default_variance,
+                      double uncertaintity_bias, double *depth1, double *variance1,
+                      void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------ helpers on the drop-in surface
+ * rust_bindings.warp.warp_vecs        (src/py/warp.rs:53-67   -> src/warp.rs:31-50)
+ * rust_bindings.interpolation.interpolation (src/py/interpolation.rs:6-16 -> src/interpolation.rs:57-73)
+ *      status (optional device int): set to 1 if any coordinate is outside [0,W-1]x[0,H-1]
+ * rust_bindings.projection.project_vecs / inv_project_vecs (src/py/projection.rs:15-43)
+ * rust_bindings.transform.transform   (src/py/transform.rs:6-16 -> src/transform.rs:9-28)
+ * rust_bindings.triangulation.calc_depth0 (src/py/triangulation.rs:7-19 -> src/triangulation.rs:22-36),
+ *      vectorised over N point pairs
+ * All take device pointers; T10 is 16 device doubles. */
+int tdk_warp_vecs_dev(const double *T10, const double *xs0, const double *depths0, int64_t n,
+                      double *xs1, double *depths1, void *stream);
+int tdk_interpolate_dev(const double *image, int64_t H, int64_t W, const double *coords, int64_t n,
+                        double *out, int32_t *status, void *stream);
+int tdk_project_vecs_dev(const double *ps, int64_t n, double *xs, void *stream);
+int tdk_inv_project_vecs_dev(const double *xs, const double *depths, int64_t n, double *ps,
+                             void *stream);
+int tdk_transform_dev(const double *T10, const double *ps0, int64_t n, double *ps1, void *stream);
+int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1, int64_t n,
+                        double *depths0, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDK_H_ */

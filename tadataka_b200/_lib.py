@@ -1,0 +1,85 @@
+"""ctypes binding of libtdk_b200.so (the C-ABI declared in include/tdk.h).
+
+There is no CPU fallback: if the shared library is missing, import fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtdk_b200.so")
+
+OK = 0
+ERR_INVALID, ERR_CUDA, ERR_AGE, ERR_SINGULAR, ERR_WORKSPACE, ERR_SEARCH_LEN, ERR_RANGE = \
+    -1, -2, -3, -4, -5, -6, -7
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -m tadataka_b200.build` "
+        "(nvcc, sm_100a).  tadataka_b200 has no CPU fallback.")
+
+lib = C.CDLL(LIB_PATH)
+
+P = C.c_void_p
+I64 = C.c_int64
+D = C.c_double
+SZ = C.c_size_t
+
+
+def _sig(name, restype, *argtypes):
+    f = getattr(lib, name)
+    f.restype = restype
+    f.argtypes = list(argtypes)
+    return f
+
+
+last_error = _sig("tdk_last_error", C.c_char_p)
+version = _sig("tdk_version", C.c_char_p)
+set_search_lanes = _sig("tdk_set_search_lanes", C.c_int, C.c_int)
+update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64)
+update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
+                        I64, I64, P, P, P, P, P, P, SZ, P)
+update_depth_frames_dev = _sig("tdk_update_depth_frames_dev", C.c_int, P, P, P, P, P, P, P, P, P,
+                               P, I64, I64, I64, I64, P, P, P, P, P, P, SZ, P)
+update_depth_status = _sig("tdk_update_depth_status", C.c_int, P, P)
+update_depth_host = _sig("tdk_update_depth_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
+                         I64, I64, P, P, P, P, P)
+estimate_debug_host = _sig("tdk_estimate_debug_host", C.c_int, P, D, D, P, P, P, P, P, P, P, I64,
+                           I64, P, P, P)
+fusion_dev = _sig("tdk_fusion_dev", C.c_int, P, P, P, P, P, I64, P, P, P)
+regularize_dev = _sig("tdk_regularize_dev", C.c_int, P, P, P, I64, I64, I64, P, P)
+increment_age_workspace_bytes = _sig("tdk_increment_age_workspace_bytes", SZ, I64, I64, I64)
+increment_age_dev = _sig("tdk_increment_age_dev", C.c_int, P, P, P, P, P, I64, I64, I64, P, P, SZ,
+                         P)
+propagate_workspace_bytes = _sig("tdk_propagate_workspace_bytes", SZ, I64, I64, I64)
+propagate_dev = _sig("tdk_propagate_dev", C.c_int, P, P, P, P, P, I64, I64, I64, D, D, D, P, P, P,
+                     SZ, P)
+warp_vecs_dev = _sig("tdk_warp_vecs_dev", C.c_int, P, P, P, I64, P, P, P)
+interpolate_dev = _sig("tdk_interpolate_dev", C.c_int, P, I64, I64, P, I64, P, P, P)
+project_vecs_dev = _sig("tdk_project_vecs_dev", C.c_int, P, I64, P, P)
+inv_project_vecs_dev = _sig("tdk_inv_project_vecs_dev", C.c_int, P, P, I64, P, P)
+transform_dev = _sig("tdk_transform_dev", C.c_int, P, P, I64, P, P)
+calc_depth0_dev = _sig("tdk_calc_depth0_dev", C.c_int, P, P, P, I64, P, P)
+
+# every symbol include/tdk.h declares (tests check the header against this list and the .so)
+EXPORTS = [
+    "tdk_last_error", "tdk_version", "tdk_set_search_lanes", "tdk_update_depth_workspace_bytes",
+    "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_status",
+    "tdk_update_depth_host", "tdk_estimate_debug_host", "tdk_fusion_dev", "tdk_regularize_dev",
+    "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",
+    "tdk_propagate_dev", "tdk_warp_vecs_dev", "tdk_interpolate_dev", "tdk_project_vecs_dev",
+    "tdk_inv_project_vecs_dev", "tdk_transform_dev", "tdk_calc_depth0_dev",
+]
+
+
+class TdkError(RuntimeError):
+    pass
+
+
+def check(rc):
+    """Map a C-ABI status to the exception the reference-facing API documents."""
+    if rc == OK:
+        return
+    msg = (last_error() or b"").decode()
+    if rc in (ERR_AGE, ERR_SINGULAR, ERR_SEARCH_LEN, ERR_RANGE, ERR_INVALID):
+        raise ValueError(msg)
+    raise TdkError(f"libtdk_b200 error {rc}: {msg}")

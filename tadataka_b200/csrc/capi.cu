@@ -1,0 +1,239 @@
+// Host-side plumbing of the C-ABI: error text, version, and the host-pointer entry points
+// (copy in -> launch -> copy out), which stage through a grow-only per-device arena and
+// pipeline chunks of keyframes over three streams so that H2D, kernels and D2H overlap.
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "tdk_common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void tdk_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int tdk_check_cuda(cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess) return TDK_OK;
+    tdk_set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return TDK_ERR_CUDA;
+}
+
+namespace {
+
+constexpr int NSTREAM = 3;
+constexpr int MAX_DEV = 64;
+
+struct Arena {
+    void *base = nullptr;
+    size_t bytes = 0;
+    cudaStream_t streams[NSTREAM] = {nullptr, nullptr, nullptr};
+    bool streams_ready = false;
+};
+Arena g_arena[MAX_DEV];
+std::mutex g_mutex;
+
+size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+
+int arena_get(size_t bytes, Arena **out)
+{
+    int dev = 0;
+    TDK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) { tdk_set_error("device index %d out of range", dev); return TDK_ERR_INVALID; }
+    Arena &ar = g_arena[dev];
+    if (!ar.streams_ready) {
+        for (int i = 0; i < NSTREAM; i++) TDK_CUDA(cudaStreamCreateWithFlags(&ar.streams[i], cudaStreamNonBlocking));
+        ar.streams_ready = true;
+    }
+    if (ar.bytes < bytes) {
+        if (ar.base) { TDK_CUDA(cudaDeviceSynchronize()); TDK_CUDA(cudaFree(ar.base)); ar.base = nullptr; ar.bytes = 0; }
+        TDK_CUDA(cudaMalloc(&ar.base, bytes));
+        ar.bytes = bytes;
+    }
+    *out = &ar;
+    return TDK_OK;
+}
+
+// per-chunk device buffers for the host path
+struct Slot {
+    double *key_imgs, *key_cams, *T_wk, *ref_imgs, *ref_cams, *T_wr, *pd, *pv, *od, *ov;
+    uint64_t *age;
+    int64_t *of;
+    int32_t *dbg;
+    uint64_t *hist;
+    void *ws;
+    size_t ws_bytes;
+};
+
+size_t carve_slot(char *base, size_t off, int64_t C, int64_t R, size_t hw, bool dbg, bool hist, Slot *s)
+{
+    auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += up256(bytes); return p; };
+    Slot t;
+    t.key_imgs = (double *)take(C * hw * 8);
+    t.key_cams = (double *)take(C * 4 * 8);
+    t.T_wk = (double *)take(C * 16 * 8);
+    t.ref_imgs = (double *)take(C * R * hw * 8);
+    t.ref_cams = (double *)take(C * R * 4 * 8);
+    t.T_wr = (double *)take(C * R * 16 * 8);
+    t.age = (uint64_t *)take(C * hw * 8);
+    t.pd = (double *)take(C * hw * 8);
+    t.pv = (double *)take(C * hw * 8);
+    t.od = (double *)take(C * hw * 8);
+    t.ov = (double *)take(C * hw * 8);
+    t.of = (int64_t *)take(C * hw * 8);
+    t.dbg = dbg ? (int32_t *)take(C * hw * 4) : nullptr;
+    t.hist = hist ? (uint64_t *)take(C * 10 * 8) : nullptr;
+    t.ws_bytes = tdk_update_depth_workspace_bytes(C, R);
+    t.ws = take(t.ws_bytes);
+    if (s) *s = t;
+    return off;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *tdk_last_error(void) { return g_err; }
+
+const char *tdk_version(void) { return "tadataka-b200 0.1.0 sm_100a"; }
+
+int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const double *T_wk,
+                          const double *ref_imgs, const double *ref_cams, const double *T_wr,
+                          const uint64_t *age, const double *prior_depth, const double *prior_variance,
+                          const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
+                          double *out_depth, double *out_variance, int64_t *out_flag,
+                          int32_t *dbg_argmin, uint64_t *out_hist)
+{
+    if (!key_imgs || !ref_imgs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
+        !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
+        tdk_set_error("tdk_update_depth_host: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    if (P <= 0 || R <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_update_depth_host: bad sizes");
+        return TDK_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lock(g_mutex);
+    const size_t hw = (size_t)H * W;
+    // chunk = as many keyframes as fit ~96 MB of staged input, so copies and kernels overlap
+    const size_t in_per_key = (size_t)(1 + R + 3) * hw * 8;
+    int64_t C = (int64_t)((96u << 20) / in_per_key);
+    if (C < 1) C = 1;
+    if (C > P) C = P;
+    const int nslots = (int)((P + C - 1) / C < NSTREAM ? (P + C - 1) / C : NSTREAM);
+    const size_t slot_bytes = carve_slot(nullptr, 0, C, R, hw, dbg_argmin != nullptr, out_hist != nullptr, nullptr);
+    Arena *ar = nullptr;
+    int rc = arena_get(slot_bytes * nslots, &ar);
+    if (rc != TDK_OK) return rc;
+    Slot slots[NSTREAM];
+    for (int i = 0; i < nslots; i++)
+        carve_slot((char *)ar->base, slot_bytes * i, C, R, hw, dbg_argmin != nullptr, out_hist != nullptr, &slots[i]);
+
+    const int64_t nchunks = (P + C - 1) / C;
+    int(*st_host)[TDK_ST_WORDS] = nullptr;
+    TDK_CUDA(cudaMallocHost((void **)&st_host, sizeof(int) * TDK_ST_WORDS * nchunks));
+    rc = TDK_OK;
+    for (int64_t c = 0; c < nchunks && rc == TDK_OK; c++) {
+        const int si = (int)(c % nslots);
+        Slot &s = slots[si];
+        cudaStream_t st = ar->streams[si];
+        const int64_t p0 = c * C, n = (p0 + C <= P) ? C : P - p0;
+#define H2D(dst, src, bytes) \
+    if (rc == TDK_OK) rc = tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st), "H2D " #src)
+#define D2H(dst, src, bytes) \
+    if (rc == TDK_OK) rc = tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st), "D2H " #src)
+        H2D(s.key_imgs, key_imgs + p0 * hw, n * hw * 8);
+        H2D(s.key_cams, key_cams + p0 * 4, n * 4 * 8);
+        H2D(s.T_wk, T_wk + p0 * 16, n * 16 * 8);
+        H2D(s.ref_imgs, ref_imgs + p0 * R * hw, n * R * hw * 8);
+        H2D(s.ref_cams, ref_cams + p0 * R * 4, n * R * 4 * 8);
+        H2D(s.T_wr, T_wr + p0 * R * 16, n * R * 16 * 8);
+        H2D(s.age, age + p0 * hw, n * hw * 8);
+        H2D(s.pd, prior_depth + p0 * hw, n * hw * 8);
+        H2D(s.pv, prior_variance + p0 * hw, n * hw * 8);
+        if (s.hist && rc == TDK_OK) rc = tdk_check_cuda(cudaMemsetAsync(s.hist, 0, n * 10 * 8, st), "memset hist");
+        if (rc == TDK_OK)
+            rc = tdk_update_depth_dev(s.key_imgs, s.key_cams, s.T_wk, s.ref_imgs, s.ref_cams, s.T_wr, s.age,
+                                      s.pd, s.pv, params, n, R, H, W, s.od, s.ov, s.of, s.dbg, s.hist, s.ws,
+                                      s.ws_bytes, st);
+        D2H(out_depth + p0 * hw, s.od, n * hw * 8);
+        D2H(out_variance + p0 * hw, s.ov, n * hw * 8);
+        D2H(out_flag + p0 * hw, s.of, n * hw * 8);
+        if (dbg_argmin) D2H(dbg_argmin + p0 * hw, s.dbg, n * hw * 4);
+        if (out_hist) D2H(out_hist + p0 * 10, s.hist, n * 10 * 8);
+        D2H(st_host[c], s.ws, sizeof(int) * TDK_ST_WORDS);
+#undef H2D
+#undef D2H
+    }
+    for (int i = 0; i < nslots; i++) {
+        const int rc2 = tdk_check_cuda(cudaStreamSynchronize(ar->streams[i]), "cudaStreamSynchronize");
+        if (rc == TDK_OK) rc = rc2;
+    }
+    if (rc == TDK_OK) {
+        for (int64_t c = 0; c < nchunks; c++) {
+            if (st_host[c][TDK_ST_SINGULAR]) { tdk_set_error("a reference pose T_wr is singular"); rc = TDK_ERR_SINGULAR; break; }
+            if (st_host[c][TDK_ST_AGE]) { tdk_set_error("Age exceeds the refframe size"); rc = TDK_ERR_AGE; break; }
+            if (st_host[c][TDK_ST_SEARCH_LEN]) {
+                tdk_set_error("an epipolar search line has more than %d samples; increase ref_step_size",
+                              TDK_MAX_SEARCH_SAMPLES);
+                rc = TDK_ERR_SEARCH_LEN;
+                break;
+            }
+        }
+    }
+    cudaFreeHost(st_host);
+    return rc;
+}
+
+int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double prior_variance,
+                            const double *key_img, const double *key_cam, const double *T_wk,
+                            const double *ref_img, const double *ref_cam, const double *T_wr,
+                            const double *params, int64_t H, int64_t W, double *out, int64_t *out_flag,
+                            int64_t *dbg)
+{
+    if (!u_key || !key_img || !key_cam || !T_wk || !ref_img || !ref_cam || !T_wr || !params || !out || !out_flag) {
+        tdk_set_error("tdk_estimate_debug_host: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    if (H <= 0 || W <= 0 || u_key[0] < 0 || u_key[0] >= W || u_key[1] < 0 || u_key[1] >= H) {
+        tdk_set_error("tdk_estimate_debug_host: u_key (%lld,%lld) outside the %lldx%lld image",
+                      (long long)u_key[0], (long long)u_key[1], (long long)W, (long long)H);
+        return TDK_ERR_RANGE;
+    }
+    // One-pixel update: age 1 at u_key, 0 elsewhere, through the same kernel as the full map.
+    const size_t hw = (size_t)H * W, at = (size_t)u_key[1] * W + u_key[0];
+    uint64_t *age = (uint64_t *)calloc(hw, 8);
+    double *pd = (double *)malloc(hw * 8), *pv = (double *)malloc(hw * 8);
+    double *od = (double *)malloc(hw * 8), *ov = (double *)malloc(hw * 8);
+    int64_t *of = (int64_t *)malloc(hw * 8);
+    int32_t *arg = (int32_t *)malloc(hw * 4);
+    int rc = TDK_OK;
+    if (!age || !pd || !pv || !od || !ov || !of || !arg) {
+        tdk_set_error("tdk_estimate_debug_host: out of host memory");
+        rc = TDK_ERR_INVALID;
+    } else {
+        for (size_t i = 0; i < hw; i++) { pd[i] = prior_depth; pv[i] = prior_variance; }
+        age[at] = 1;
+        rc = tdk_update_depth_host(key_img, key_cam, T_wk, ref_img, ref_cam, T_wr, age, pd, pv, params, 1, 1,
+                                   H, W, od, ov, of, arg, nullptr);
+        if (rc == TDK_OK) {
+            *out_flag = of[at];
+            // py/semi_dense.rs:138-154: the prior is echoed untouched on any failure
+            out[0] = of[at] == TDK_FLAG_SUCCESS ? od[at] : prior_depth;
+            out[1] = of[at] == TDK_FLAG_SUCCESS ? ov[at] : prior_variance;
+            if (dbg) dbg[0] = arg[at];
+        }
+    }
+    free(age); free(pd); free(pv); free(od); free(ov); free(of); free(arg);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,491 @@
+// Companion kernels of the semi-dense path: Gaussian fusion, 3x3 validity-weighted
+// regularisation, age-map increment and depth/variance propagation.
+// All of them are streaming or scatter kernels bound by HBM; see DESIGN.md for bytes/pixel.
+#include <math.h>
+
+#include "tdk_common.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+
+// ------------------------------------------------------------------------------------ fusion
+// fusion.rs:3-11 : mu = (mu1*v2 + mu2*v1)/(v1+v2), var = v1*v2/(v1+v2)
+__global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ mu1,
+                                                     const double *__restrict__ mu2,
+                                                     const double *__restrict__ var1,
+                                                     const double *__restrict__ var2,
+                                                     const long long *__restrict__ flag, size_t n,
+                                                     double *__restrict__ mu, double *__restrict__ var)
+{
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const double m1 = mu1[i], v1 = var1[i];
+        if (flag && flag[i] != TDK_FLAG_SUCCESS) {
+            mu[i] = m1;
+            var[i] = v1;
+            continue;
+        }
+        const double m2 = mu2[i], v2 = var2[i];
+        const double v = v1 + v2;
+        mu[i] = (m1 * v2 + m2 * v1) / v;
+        var[i] = (v1 * v2) / v;
+    }
+}
+
+// -------------------------------------------------------------------------------- regularize
+// regularization.rs:29-64 : sum over the zero-padded 3x3 (row-major) of id*iv / sum of iv where
+// flag == Success; no Success cell -> the input depth is kept.
+__global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restrict__ depth,
+                                                         const double *__restrict__ variance,
+                                                         const long long *__restrict__ flag, int P, int H,
+                                                         int W, double *__restrict__ out)
+{
+    const int x = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    const int p = blockIdx.z;
+    if (x >= W || y >= H) return;
+    const size_t base = (size_t)p * H * W;
+    double num = 0., den = 0.;
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++) {
+#pragma unroll
+        for (int dx = -1; dx <= 1; dx++) {
+            const int yy = y + dy, xx = x + dx;
+            if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+            const size_t i = base + (size_t)yy * W + xx;
+            if (__ldg(flag + i) != TDK_FLAG_SUCCESS) continue;
+            const double id = tdk::inv(__ldg(depth + i));
+            const double iv = tdk::inv(__ldg(variance + i));
+            num = num + id * iv;
+            den = den + iv;
+        }
+    }
+    const size_t c = base + (size_t)y * W + x;
+    out[c] = den == 0. ? depth[c] : tdk::inv(num / den);
+}
+
+// ------------------------------------------------------------------- forward warp of a pixel
+// PerspectiveWarp (warp.rs:72-85): K1 * pi(T10 * pi^-1(K0^-1 u0, depth0)); returns the target's
+// linear index inside the frame or -1 when the float coordinates fall outside the image
+// (image_range.rs:10-17; the truncation is propagation.rs:73 / age.rs:27).
+struct FrameConst {
+    double T[12];
+    double f0x, f0y, o0x, o0y, f1x, f1y, o1x, o1y;
+};
+
+__device__ __forceinline__ FrameConst load_frame_const(const double *__restrict__ T10,
+                                                       const double *__restrict__ cam0,
+                                                       const double *__restrict__ cam1, int p)
+{
+    FrameConst c;
+#pragma unroll
+    for (int i = 0; i < 12; i++) c.T[i] = __ldg(T10 + 16 * (size_t)p + i);
+    c.f0x = __ldg(cam0 + 4 * p); c.f0y = __ldg(cam0 + 4 * p + 1);
+    c.o0x = __ldg(cam0 + 4 * p + 2); c.o0y = __ldg(cam0 + 4 * p + 3);
+    c.f1x = __ldg(cam1 + 4 * p); c.f1y = __ldg(cam1 + 4 * p + 1);
+    c.o1x = __ldg(cam1 + 4 * p + 2); c.o1y = __ldg(cam1 + 4 * p + 3);
+    return c;
+}
+
+__device__ __forceinline__ int warp_target(const FrameConst &c, int x0, int y0, double depth0, int H,
+                                           int W, double &depth1)
+{
+    const double qx = ((double)x0 - c.o0x) / c.f0x;
+    const double qy = ((double)y0 - c.o0y) / c.f0y;
+    double x1, y1;
+    tdk::warp_point(c.T, qx, qy, depth0, x1, y1, depth1);
+    const double u = x1 * c.f1x + c.o1x;
+    const double v = y1 * c.f1y + c.o1y;
+    if (!tdk::in_range(u, v, (double)W - 1., (double)H - 1.)) return -1;
+    return (int)v * W + (int)u;
+}
+
+// ----------------------------------------------------------------------------- increment_age
+// age.rs:6-32.  The raster-order "last writer wins" becomes: the winner of a target is the source
+// with the largest linear index (atomicMax), then one gather pass writes age0[winner] + 1.
+__global__ void __launch_bounds__(TPB) age_scatter_kernel(const double *__restrict__ T10,
+                                                          const double *__restrict__ cam0,
+                                                          const double *__restrict__ cam1,
+                                                          const double *__restrict__ depth0, int H, int W,
+                                                          unsigned int *__restrict__ winner)
+{
+    const int p = blockIdx.y;
+    const int hw = H * W;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= hw) return;
+    const FrameConst c = load_frame_const(T10, cam0, cam1, p);
+    double d1;
+    const int t = warp_target(c, s % W, s / W, depth0[(size_t)p * hw + s], H, W, d1);
+    if (t >= 0) atomicMax(winner + (size_t)p * hw + t, (unsigned int)s + 1u);
+}
+
+__global__ void __launch_bounds__(TPB) age_gather_kernel(const uint64_t *__restrict__ age0,
+                                                         const unsigned int *__restrict__ winner, int hw,
+                                                         uint64_t *__restrict__ age1)
+{
+    const int p = blockIdx.y;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= hw) return;
+    const unsigned int w = winner[(size_t)p * hw + t];
+    age1[(size_t)p * hw + t] = w ? age0[(size_t)p * hw + (w - 1u)] + 1ull : 0ull;
+}
+
+// --------------------------------------------------------------------------------- propagate
+// propagation.rs:48-92.  The reference folds colliding sources into a HashMap in raster order;
+// the fold is order dependent (gated fusion, nearer-depth-wins), so the GPU builds, per target,
+// the list of its sources (count -> exclusive scan -> fill), sorts each list by source index and
+// replays the same fold sequentially.
+__global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restrict__ T10,
+                                                         const double *__restrict__ cam0,
+                                                         const double *__restrict__ cam1,
+                                                         const double *__restrict__ depth0, int H, int W,
+                                                         int *__restrict__ tgt, unsigned int *__restrict__ cnt)
+{
+    const int p = blockIdx.y;
+    const int hw = H * W;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= hw) return;
+    const FrameConst c = load_frame_const(T10, cam0, cam1, p);
+    double d1;
+    const int t = warp_target(c, s % W, s / W, depth0[(size_t)p * hw + s], H, W, d1);
+    tgt[(size_t)p * hw + s] = t;
+    if (t >= 0) atomicAdd(cnt + (size_t)p * hw + t, 1u);
+}
+
+// exclusive scan of n u32 values, 1024 per block: (a) block sums, (b) scan of the sums by one
+// block, (c) block-local scan + offset.  out has n+1 entries; out[n] = total.
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = TPB * SCAN_ITEMS;
+
+__device__ __forceinline__ unsigned int block_exclusive_scan(unsigned int v, unsigned int *s_warp,
+                                                             unsigned int &total)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned int incl = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += o;
+    }
+    if (lane == 31) s_warp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        unsigned int w = lane < (int)(blockDim.x >> 5) ? s_warp[lane] : 0u;
+        unsigned int wi = w;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const unsigned int o = __shfl_up_sync(0xffffffffu, wi, off);
+            if (lane >= off) wi += o;
+        }
+        s_warp[lane] = wi - w;            // exclusive warp offsets
+        if (lane == 31) s_warp[32] = wi;  // block total
+    }
+    __syncthreads();
+    total = s_warp[32];
+    const unsigned int r = incl - v + s_warp[wid];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(TPB) scan_sums_kernel(const unsigned int *__restrict__ in, size_t n,
+                                                        unsigned int *__restrict__ bsum)
+{
+    __shared__ unsigned int s_warp[33];
+    const size_t base = (size_t)blockIdx.x * SCAN_TILE;
+    unsigned int v = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const size_t i = base + (size_t)k * TPB + threadIdx.x;
+        if (i < n) v += in[i];
+    }
+    unsigned int total;
+    block_exclusive_scan(v, s_warp, total);
+    if (threadIdx.x == 0) bsum[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) scan_bsum_kernel(unsigned int *__restrict__ bsum, size_t m,
+                                                         unsigned int *__restrict__ total_out)
+{
+    __shared__ unsigned int s_warp[33];
+    unsigned int carry = 0;
+    for (size_t base = 0; base < m; base += 1024) {
+        const size_t i = base + threadIdx.x;
+        const unsigned int v = i < m ? bsum[i] : 0u;
+        unsigned int total;
+        const unsigned int ex = block_exclusive_scan(v, s_warp, total);
+        if (i < m) bsum[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) *total_out = carry;
+}
+
+__global__ void __launch_bounds__(TPB) scan_apply_kernel(const unsigned int *__restrict__ in, size_t n,
+                                                         const unsigned int *__restrict__ bsum,
+                                                         unsigned int *__restrict__ out)
+{
+    __shared__ unsigned int s_warp[33];
+    const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    unsigned int v[SCAN_ITEMS], sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        v[k] = base + k < n ? in[base + k] : 0u;
+        sum += v[k];
+    }
+    unsigned int total;
+    unsigned int run = block_exclusive_scan(sum, s_warp, total) + bsum[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        if (base + k < n) out[base + k] = run;
+        run += v[k];
+    }
+}
+
+__global__ void __launch_bounds__(TPB) prop_fill_kernel(const int *__restrict__ tgt,
+                                                        unsigned int *__restrict__ cnt,
+                                                        const unsigned int *__restrict__ off, int hw,
+                                                        unsigned int *__restrict__ list)
+{
+    const int p = blockIdx.y;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= hw) return;
+    const int t = tgt[(size_t)p * hw + s];
+    if (t < 0) return;
+    const size_t g = (size_t)p * hw + t;
+    const unsigned int slot = atomicSub(cnt + g, 1u) - 1u;
+    list[off[g] + slot] = (unsigned int)s;
+}
+
+__device__ __forceinline__ void sift_down(unsigned int *a, unsigned int start, unsigned int end)
+{
+    unsigned int root = start;
+    while (2u * root + 1u <= end) {
+        unsigned int child = 2u * root + 1u, sw = root;
+        if (a[sw] < a[child]) sw = child;
+        if (child + 1u <= end && a[sw] < a[child + 1u]) sw = child + 1u;
+        if (sw == root) return;
+        const unsigned int tmp = a[root];
+        a[root] = a[sw];
+        a[sw] = tmp;
+        root = sw;
+    }
+}
+
+__global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict__ T10,
+                                                        const double *__restrict__ cam0,
+                                                        const double *__restrict__ cam1,
+                                                        const double *__restrict__ depth0,
+                                                        const double *__restrict__ variance0, int H, int W,
+                                                        const unsigned int *__restrict__ off,
+                                                        unsigned int *__restrict__ list, double def_d,
+                                                        double def_v, double bias, double *__restrict__ depth1,
+                                                        double *__restrict__ variance1)
+{
+    const int p = blockIdx.y;
+    const int hw = H * W;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= hw) return;
+    const size_t g = (size_t)p * hw + t;
+    const unsigned int b = off[g], k = off[g + 1] - b;
+    if (k == 0) {
+        depth1[g] = def_d;
+        variance1[g] = def_v;
+        return;
+    }
+    unsigned int *seg = list + b;
+    if (k > 1) {
+        if (k <= 16) {   // insertion sort: the common case is 2..4 sources per target
+            for (unsigned int i = 1; i < k; i++) {
+                const unsigned int key = seg[i];
+                unsigned int j = i;
+                while (j > 0 && seg[j - 1] > key) { seg[j] = seg[j - 1]; j--; }
+                seg[j] = key;
+            }
+        } else {         // heap sort keeps degenerate many-to-one warps O(k log k)
+            for (int start = (int)(k - 2) / 2; start >= 0; start--) sift_down(seg, (unsigned int)start, k - 1);
+            for (unsigned int end = k - 1; end > 0; end--) {
+                const unsigned int tmp = seg[end];
+                seg[end] = seg[0];
+                seg[0] = tmp;
+                sift_down(seg, 0, end - 1);
+            }
+        }
+    }
+    const FrameConst c = load_frame_const(T10, cam0, cam1, p);
+    double acc_d = 0., acc_v = 0.;
+    for (unsigned int i = 0; i < k; i++) {
+        const unsigned int s = seg[i];
+        const double d0 = depth0[(size_t)p * hw + s], v0 = variance0[(size_t)p * hw + s];
+        double d1a;
+        warp_target(c, (int)(s % W), (int)(s / W), d0, H, W, d1a);
+        // propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
+        const double ratio = tdk::inv(d1a) / tdk::inv(d0);
+        const double r2 = ratio * ratio;
+        const double v1a = (r2 * r2) * v0 + bias;
+        if (i == 0) { acc_d = d1a; acc_v = v1a; continue; }
+        // handle_collision(a = new, b = stored), propagation.rs:21-46 ; stat.rs:5-26 ; fusion.rs:3-11
+        const double ia = tdk::inv(d1a), ib = tdk::inv(acc_d);
+        const double ds = (ia - ib) * (ia - ib);
+        const double fs = TDK_STAT_FACTOR * TDK_STAT_FACTOR;
+        if (ds <= fs * v1a && ds <= fs * acc_v) {
+            const double v = v1a + acc_v;
+            const double mu = (ia * acc_v + ib * v1a) / v;
+            acc_d = tdk::inv(mu);
+            acc_v = (v1a * acc_v) / v;
+        } else if (d1a < acc_d) {
+            acc_d = d1a;
+            acc_v = v1a;
+        }
+    }
+    depth1[g] = acc_d;
+    variance1[g] = acc_v;
+}
+
+size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+
+struct PropLayout {
+    size_t tgt, cnt, off, list, bsum, total;
+};
+PropLayout prop_layout(int64_t P, int64_t H, int64_t W)
+{
+    const size_t n = (size_t)P * H * W;
+    const size_t m = (n + SCAN_TILE - 1) / SCAN_TILE;
+    PropLayout l;
+    size_t o = 0;
+    l.tgt = o; o = up256(o + n * 4);
+    l.cnt = o; o = up256(o + n * 4);
+    l.off = o; o = up256(o + (n + 1) * 4);
+    l.list = o; o = up256(o + n * 4);
+    l.bsum = o; o = up256(o + (m + 1) * 4);
+    l.total = o;
+    return l;
+}
+
+int check_frames(const char *who, int64_t P, int64_t H, int64_t W)
+{
+    if (P <= 0 || H <= 0 || W <= 0 || P > 65535 || H * W > 0x7fffffffLL / 2 ||
+        (double)P * (double)H * (double)W >= 4294967295.0) {
+        tdk_set_error("%s: bad sizes P=%lld H=%lld W=%lld", who, (long long)P, (long long)H, (long long)W);
+        return TDK_ERR_INVALID;
+    }
+    return TDK_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tdk_fusion_dev(const double *mu1, const double *mu2, const double *var1, const double *var2,
+                   const int64_t *flag, int64_t n, double *mu, double *var, void *stream)
+{
+    if (!mu1 || !mu2 || !var1 || !var2 || !mu || !var || n < 0) {
+        tdk_set_error("tdk_fusion_dev: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    if (n == 0) return TDK_OK;
+    long long blocks = (n + TPB - 1) / TPB;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    fusion_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(mu1, mu2, var1, var2, (const long long *)flag,
+                                                                     (size_t)n, mu, var);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_regularize_dev(const double *depth, const double *variance, const int64_t *flag, int64_t P, int64_t H,
+                       int64_t W, double *out_depth, void *stream)
+{
+    if (!depth || !variance || !flag || !out_depth) {
+        tdk_set_error("tdk_regularize_dev: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    int rc = check_frames("tdk_regularize_dev", P, H, W);
+    if (rc != TDK_OK) return rc;
+    dim3 grid((unsigned)((W + 63) / 64), (unsigned)((H + 3) / 4), (unsigned)P);
+    regularize_kernel<<<grid, TPB, 0, (cudaStream_t)stream>>>(depth, variance, (const long long *)flag, (int)P,
+                                                              (int)H, (int)W, out_depth);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+size_t tdk_increment_age_workspace_bytes(int64_t P, int64_t H, int64_t W)
+{
+    if (P <= 0 || H <= 0 || W <= 0) return 0;
+    return up256((size_t)P * H * W * 4);
+}
+
+int tdk_increment_age_dev(const uint64_t *age0, const double *cam0, const double *cam1, const double *T10,
+                          const double *depth0, int64_t P, int64_t H, int64_t W, uint64_t *age1,
+                          void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (!age0 || !cam0 || !cam1 || !T10 || !depth0 || !age1 || !workspace) {
+        tdk_set_error("tdk_increment_age_dev: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    int rc = check_frames("tdk_increment_age_dev", P, H, W);
+    if (rc != TDK_OK) return rc;
+    if (workspace_bytes < tdk_increment_age_workspace_bytes(P, H, W)) {
+        tdk_set_error("tdk_increment_age_dev: workspace too small");
+        return TDK_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int hw = (int)(H * W);
+    unsigned int *winner = (unsigned int *)workspace;
+    TDK_CUDA(cudaMemsetAsync(winner, 0, (size_t)P * hw * 4, st));
+    dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
+    age_scatter_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, winner);
+    TDK_CUDA(cudaGetLastError());
+    age_gather_kernel<<<grid, TPB, 0, st>>>(age0, winner, hw, age1);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+size_t tdk_propagate_workspace_bytes(int64_t P, int64_t H, int64_t W)
+{
+    if (P <= 0 || H <= 0 || W <= 0) return 0;
+    return prop_layout(P, H, W).total;
+}
+
+int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1, const double *depth0,
+                      const double *variance0, int64_t P, int64_t H, int64_t W, double default_depth,
+                      double default_variance, double uncertaintity_bias, double *depth1, double *variance1,
+                      void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || !workspace) {
+        tdk_set_error("tdk_propagate_dev: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    int rc = check_frames("tdk_propagate_dev", P, H, W);
+    if (rc != TDK_OK) return rc;
+    const PropLayout l = prop_layout(P, H, W);
+    if (workspace_bytes < l.total) {
+        tdk_set_error("tdk_propagate_dev: workspace %zu < required %zu", workspace_bytes, l.total);
+        return TDK_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws = (char *)workspace;
+    int *tgt = (int *)(ws + l.tgt);
+    unsigned int *cnt = (unsigned int *)(ws + l.cnt), *off = (unsigned int *)(ws + l.off);
+    unsigned int *list = (unsigned int *)(ws + l.list), *bsum = (unsigned int *)(ws + l.bsum);
+    const int hw = (int)(H * W);
+    const size_t n = (size_t)P * hw;
+    const size_t m = (n + SCAN_TILE - 1) / SCAN_TILE;
+    TDK_CUDA(cudaMemsetAsync(cnt, 0, n * 4, st));
+    dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
+    prop_count_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, tgt, cnt);
+    TDK_CUDA(cudaGetLastError());
+    scan_sums_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum);
+    TDK_CUDA(cudaGetLastError());
+    scan_bsum_kernel<<<1, 1024, 0, st>>>(bsum, m, off + n);
+    TDK_CUDA(cudaGetLastError());
+    scan_apply_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum, off);
+    TDK_CUDA(cudaGetLastError());
+    prop_fill_kernel<<<grid, TPB, 0, st>>>(tgt, cnt, off, hw, list);
+    TDK_CUDA(cudaGetLastError());
+    prop_fold_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, variance0, (int)H, (int)W, off, list,
+                                           default_depth, default_variance, uncertaintity_bias, depth1,
+                                           variance1);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+}  // extern "C"

@@ -19,6 +19,7 @@ from scipy.spatial.transform import Rotation
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 import oracle as ora  # noqa: E402
+from tests.golden_util import rgb2gray  # noqa: E402
 
 ROOT = "/root/reference/tests/dataset/new_tsukuba"
 
@@ -26,12 +27,6 @@ ROOT = "/root/reference/tests/dataset/new_tsukuba"
 def load_rgb(path):
     bgra = cv2.imread(path, cv2.IMREAD_UNCHANGED)
     return np.ascontiguousarray(bgra[:, :, 2::-1])  # -> RGB, alpha dropped (new_tsukuba.py:85-86)
-
-
-def rgb2gray(rgb):
-    """skimage.color.rgb2gray on a uint8 image (skimage is not installed here)."""
-    f = rgb.astype(np.float64) / 255.
-    return f @ np.array([0.2125, 0.7154, 0.0721])
 
 
 def poses():

@@ -1,0 +1,81 @@
+"""The C-ABI library loads and exports every symbol include/tdk.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "tdk.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(tdk_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from tadataka_b200 import _lib
+    names = declared_symbols()
+    assert len(names) >= 20
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/tdk.h but not exported"
+    assert sorted(_lib.EXPORTS) == names
+
+
+def test_version_and_error_text_without_a_gpu():
+    from tadataka_b200 import _lib
+    assert b"sm_100a" in _lib.version()
+    # argument validation happens before any CUDA call
+    assert _lib.set_search_lanes(7) == _lib.ERR_INVALID
+    assert b"not in {8,16,32}" in _lib.last_error()
+    assert _lib.update_depth_workspace_bytes(0, 1) == 0
+    assert _lib.update_depth_workspace_bytes(4, 8) > 0
+    assert _lib.propagate_workspace_bytes(1, 480, 640) >= 4 * 4 * 480 * 640
+
+
+def test_reference_module_surface():
+    """The eight rust_bindings modules and the names the reference's Python imports from them
+    (src/py/*.rs #[pymodule] blocks)."""
+    import importlib
+    surface = {
+        "semi_dense": ["Frame", "Params", "estimate_debug_", "increment_age", "update_depth",
+                       "propagate"],
+        "camera": ["CameraParameters"],
+        "warp": ["warp_vec", "warp_vecs"],
+        "interpolation": ["interpolation"],
+        "projection": ["project_vec", "project_vecs", "inv_project_vec", "inv_project_vecs"],
+        "transform": ["transform"],
+        "triangulation": ["calc_depth0"],
+        "homogeneous": ["to_homogeneous_vec", "to_homogeneous_vecs", "from_homogeneous_vec",
+                        "from_homogeneous_vecs"],
+    }
+    for mod, names in surface.items():
+        m = importlib.import_module("rust_bindings." + mod)
+        for n in names:
+            assert hasattr(m, n), f"rust_bindings.{mod}.{n} missing"
+    from tadataka.vo.semi_dense.flag import ResultFlag
+    assert [int(f) for f in ResultFlag] == list(range(0, -10, -1))
+
+
+def test_frame_and_params_constructors():
+    # tests/vo/semi_dense/test_semi_dense.py:16-31
+    import numpy as np
+    import pytest
+    from rust_bindings.camera import CameraParameters
+    from rust_bindings.semi_dense import Frame, Params
+    cp = CameraParameters((10., 10.), (20., 10.))
+    frame = Frame(cp, np.zeros((40, 20)), np.zeros((4, 4)))
+    assert frame.image.shape == (40, 20) and frame.transform_wf.shape == (4, 4)
+    assert frame.camera_params.focal_length.tolist() == [10., 10.]
+    assert frame.camera_params.offset.dtype == np.float64
+    Params(min_depth=0.1, max_depth=10.0, geo_coeff=0.4, photo_coeff=0.5, ref_step_size=0.02,
+           min_gradient=0.001)
+    Params(0.1, 10.0, 0.4, 0.5, 0.02, 0.001)
+    with pytest.raises(TypeError):     # exact-dtype extraction, like pyo3-numpy
+        Frame(cp, np.zeros((40, 20), dtype=np.float32), np.zeros((4, 4)))
+    # any object with float64 .focal_length / .offset works (duck typing, py/semi_dense.rs:19-33)
+
+    class Duck:
+        focal_length = np.array([1., 2.])
+        offset = np.array([3., 4.])
+    assert Frame(Duck(), np.zeros((4, 4)), np.eye(4)).camera_params.offset.tolist() == [3., 4.]
