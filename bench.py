@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- semi-dense depth updates (pixels/sec) at 640x480, the metric of BASELINE.json.
+
+Workload (BASELINE.json configs[1], SURVEY 8d "C2"), per GPU and per step:
+    B keyframes 640x480, each matched against 8 reference frames (one per pixel, chosen by the
+    pixel's age in 32x32 blocks, age 0 = not processed), successful measurements fused with the
+    prior by Gaussian fusion in inverse depth.  Synthetic piecewise-planar scenes
+    (tadataka_b200/scene.py), f64 images and maps as the reference stores them.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    (N > 1: launched by `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N`;
+     a plain `python bench.py --gpus N` re-launches itself that way.)
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = the same step through
+the host-pointer C-ABI call (tdk_update_depth_host) from pinned host buffers, H2D and D2H inside
+the timed region; `roofline` = algorithmic bytes of the dominant kernel / its CUDA-event time vs
+the measured HBM peak; `cpu_baseline` = the oracle (CPU restatement of the reference) on the host.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H, W, R = 480, 640, 8
+METRIC = "semi-dense depth updates (pixels/sec) at 640x480"
+UNIT = "pixels/s"
+# key 8 + one reference 8 + prior depth 8 + prior variance 8 + age 8 read,
+# depth 8 + variance 8 + flag 8 written (each pixel uses ONE reference, chosen by age)
+ALGO_BYTES_PER_PX = 64
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--keyframes", type=int, default=64, help="keyframes per GPU per step")
+    ap.add_argument("--distinct", type=int, default=8, help="distinct rendered scenes per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=0, help="search lanes override (8/16/32)")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------- workload
+def make_workload(rank, B, distinct):
+    """B keyframes: `distinct` rendered scenes, each reused for B/distinct keyframes with its own
+    seeded age map and priors (every keyframe is a separate copy in memory)."""
+    from tadataka_b200 import scene
+    distinct = max(1, min(distinct, B))
+    base = [scene.make_keyframe(2000 + 1000 * rank + i, R=R, H=H, W=W) for i in range(distinct)]
+    items = []
+    for k in range(B):
+        src = base[k % distinct]
+        if k < distinct:
+            items.append(src)
+            continue
+        rng = np.random.default_rng(7_000_000 + 10_000 * rank + k)
+        it = dict(src)
+        blocks = rng.integers(0, R + 1, size=((H + 31) // 32, (W + 31) // 32))
+        it["age"] = np.ascontiguousarray(
+            np.kron(blocks, np.ones((32, 32), dtype=np.int64))[:H, :W].astype(np.uint64))
+        lo, hi = src["params"][0], src["params"][1]
+        it["prior_depth"] = np.clip(src["gt_depth"] * (1.0 + rng.uniform(-0.1, 0.1, size=(H, W))),
+                                    lo * 1.01, hi * 0.99)
+        it["prior_variance"] = 10.0 ** rng.uniform(-3.0, 0.0, size=(H, W))
+        items.append(it)
+    return scene.stack_keyframes(items)
+
+
+def cpu_pipeline(ora, b, sl, threads):
+    """The oracle's version of one step on keyframes b[sl]: update_depth + Gaussian fusion."""
+    d, v, f = ora.update_depth_batch(b["key_img"][sl], b["key_cam"][sl], b["T_wk"][sl],
+                                     b["ref_imgs"][sl], b["ref_cams"][sl], b["T_wr"][sl],
+                                     b["age"][sl], b["prior_depth"][sl], b["prior_variance"][sl],
+                                     ora.make_params(*b["params"]), threads=threads)
+    eps = np.finfo(np.float64).eps
+    pd, pv = b["prior_depth"][sl], b["prior_variance"][sl]
+    ok = f == 0
+    with np.errstate(all="ignore"):
+        ia, ib = 1. / (pd[ok] + eps), 1. / (d[ok] + eps)
+        vs = pv[ok] + v[ok]
+        d[ok] = 1. / ((ia * v[ok] + ib * pv[ok]) / vs + eps)
+        v[ok] = (pv[ok] * v[ok]) / vs
+    return d, v, f
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def time_cpu(ora, b, n_keyframes, threads, budget_s=20.0, max_reps=5):
+    sl = slice(0, n_keyframes)
+    cpu_pipeline(ora, b, slice(0, min(n_keyframes, threads)), threads)      # warm-up
+    best, spent, reps = None, 0.0, 0
+    while reps < max_reps and (reps < 2 or spent < budget_s):
+        t0 = time.perf_counter()
+        cpu_pipeline(ora, b, sl, threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+        spent += dt
+        reps += 1
+    return n_keyframes * H * W / best, best, reps
+
+
+# --------------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+    BAD = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+           "hw_power_brake_slowdown": 0x80}
+    NOTE = {"sw_power_cap": 0x4}
+
+    def __init__(self, index, period=0.002):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.stop_flag = [], set(), False
+        self.max_mhz, self.ok = None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        while not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for name, bit in {**self.BAD, **self.NOTE}.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def result(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def profiled_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of update_depth_kernel from the
+    committed ncu --set full capture of this same workload (profiles/traffic.json), else None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t.get("update_depth_kernel_bytes_per_px")
+    except Exception:
+        return None
+
+
+# --------------------------------------------------------------------------------- arms
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path.  The Rust crate cannot be built in this image
+    (no cargo/rustc), so this is the oracle port (oracle/tdk_oracle.c), all host threads."""
+    if rank != 0:
+        return
+    import oracle as ora
+    threads = host_threads()
+    b = make_workload(0, max(threads, min(args.keyframes, 2 * threads)), args.distinct)
+    P = b["key_img"].shape[0]
+    # size the per-step sample so that the whole run stays within ~2 minutes
+    t0 = time.perf_counter()
+    cpu_pipeline(ora, b, slice(0, min(P, threads)), threads)
+    t_unit = (time.perf_counter() - t0) / min(P, threads) * threads   # thread-seconds per keyframe
+    total_steps = args.steps + args.warmup
+    S = int(max(1, min(P, (120.0 * threads / max(t_unit, 1e-6)) / max(total_steps, 1))))
+    if S >= threads:
+        S = S // threads * threads
+    sl = slice(0, S)
+    for _ in range(args.warmup):
+        cpu_pipeline(ora, b, sl, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_pipeline(ora, b, sl, threads)
+    dt = time.perf_counter() - t0
+    value = S * H * W * args.steps / dt
+    sample = f"{S} of {args.keyframes} keyframes per step (640x480, 8 refs by age, fusion), {threads} threads"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "ms_per_keyframe": 1e3 * dt / args.steps / S, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"C2: {args.keyframes} x (640x480 keyframe vs 8 reference frames by "
+                               "age + Gaussian fusion) per step", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from tadataka_b200 import _lib, device
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; tadataka_b200 has no CPU path "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.lanes:
+        _lib.check(_lib.set_search_lanes(args.lanes))
+
+    B = args.keyframes
+    b = make_workload(rank, B, args.distinct)
+    names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
+             "prior_variance"]
+    pinned = {k: torch.from_numpy(b[k]).pin_memory() for k in names}
+    t = {k: pinned[k].to(dev, non_blocking=True) for k in names}
+    params = np.ascontiguousarray(b["params"], dtype=np.float64)
+    out = (torch.empty((B, H, W), dtype=torch.float64, device=dev),
+           torch.empty((B, H, W), dtype=torch.float64, device=dev),
+           torch.empty((B, H, W), dtype=torch.int64, device=dev))
+    torch.cuda.synchronize()
+
+    def step():
+        device.update_depth(t["key_img"], t["key_cam"], t["T_wk"], t["ref_imgs"], t["ref_cams"],
+                            t["T_wr"], t["age"], t["prior_depth"], t["prior_variance"], params,
+                            check=False, out=out, fuse=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    # status of the warm-up launches (age / pose / search-length errors would show here)
+    ws = device.workspace(_lib.update_depth_workspace_bytes(B, R), dev, "update_depth")
+    _lib.check(_lib.update_depth_status(C.c_void_p(ws.data_ptr()),
+                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+    sampler = ClockSampler(local_rank)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    sampler.stop_flag = True
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    sampler.join(timeout=1.0)
+
+    # ---- e2e: host-pointer C-ABI call, pinned host buffers, copies inside the timed region
+    e2e_steps = args.e2e_steps or min(args.steps, 10)
+    h_out = (torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
+             torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
+             torch.empty((B, H, W), dtype=torch.int64).pin_memory())
+
+    def vp(x):
+        return C.c_void_p(x.data_ptr())
+
+    def e2e_step():
+        rc = _lib.update_depth_host(vp(pinned["key_img"]), vp(pinned["key_cam"]), vp(pinned["T_wk"]),
+                                    vp(pinned["ref_imgs"]), vp(pinned["ref_cams"]), vp(pinned["T_wr"]),
+                                    vp(pinned["age"]), vp(pinned["prior_depth"]),
+                                    vp(pinned["prior_variance"]), params.ctypes.data_as(C.c_void_p),
+                                    B, R, H, W, vp(h_out[0]), vp(h_out[1]), vp(h_out[2]), None, None, 1)
+        _lib.check(rc)
+
+    e2e_step()
+    e2e_step()
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    h2d = sum(pinned[k].numel() * pinned[k].element_size() for k in names)
+    d2h = sum(x.numel() * x.element_size() for x in h_out)
+    # the e2e path must give the same answer as the resident path
+    same = bool(torch.equal(h_out[0], out[0].cpu()) and torch.equal(h_out[2], out[2].cpu()))
+
+    # ---- aggregate over ranks (max time), optional NCCL gather of the maps (never in the loop)
+    gather_ms = None
+    if world > 1:
+        tm = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ms_total, e2e_s = float(tm[0]), float(tm[1])
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        gathered = torch.empty((world, B, H, W), dtype=torch.float64, device=dev)
+        hist = (out[2] == 0).sum().reshape(1)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g0.record()
+        dist.all_gather_into_tensor(gathered, out[0])
+        dist.all_reduce(hist)
+        g1.record()
+        torch.cuda.synchronize()
+        gather_ms = g0.elapsed_time(g1)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    px_step = B * H * W
+    ms_step = ms_total / args.steps
+    value = world * px_step * args.steps / (ms_total * 1e-3)
+    peak, peak_src = measured_peak()
+    achieved = ALGO_BYTES_PER_PX * px_step / (ms_step * 1e-3) / 1e9
+    traffic_px = profiled_traffic()
+    n_success = int((out[2] == 0).sum())
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_keyframe": ms_step / B,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {
+            "workload": f"C2: {B} x (640x480 keyframe vs 8 reference frames by age + Gaussian "
+                        "fusion) per GPU per step",
+            "keyframes_per_gpu": B, "refs": R, "distinct_scenes": min(args.distinct, B),
+            "l2": f"inputs {h2d / 1e9:.2f} GB per step >> 126 MB L2 (no flush needed)",
+            "success_px_per_step": n_success, "success_px_per_s": world * n_success / (ms_step * 1e-3),
+            "params": [float(x) for x in params], "e2e_matches_resident": same,
+            "nccl_gather_ms": gather_ms,
+        },
+        "roofline": {
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "peak_source": peak_src,
+            "traffic": None if traffic_px is None else traffic_px * px_step,
+            "kernel": "update_depth_kernel (step time incl. the ~us pair_setup_kernel)",
+            "algorithmic_bytes_per_px": ALGO_BYTES_PER_PX,
+        },
+        "clocks": sampler.result(),
+        "e2e": {"value": world * px_step * e2e_steps / e2e_s, "unit": UNIT,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                "api": "tdk_update_depth_host (pinned host buffers, fuse_on_success=1)"},
+        "gpu_launches": 2 * args.steps,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        import oracle as ora
+        threads = host_threads()
+        n_kf = min(B, max(threads, 8))
+        v, best, reps = time_cpu(ora, b, n_kf, threads)
+        line["cpu_baseline"] = {
+            "value": v, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{n_kf} of the step's {B} keyframes, best of {reps} runs, "
+                      f"{1e3 * best / n_kf:.2f} ms/keyframe, OpenMP over keyframes"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def main():
+    args = parse()
+    if args.gpus > 1 and "RANK" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+               f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1", "--master-port",
+               str(free_port()), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -76,6 +76,12 @@ const char *tdk_version(void);
  *   dbg_argmin (optional) [P,H,W] i32: search result argmin+2 (intensities.rs:32-36), -1 where no
  *       search ran -- the "extra debug output" the parity gate compares
  *   out_hist (optional) [P,10] u64: per-keyframe count of each flag, index = -flag; ADDED to
+ *   fuse_on_success: 0 = the reference's update_depth (the NEW measurement is returned, F5);
+ *       1 = where the flag is SUCCESS the measurement is fused with the prior in inverse depth,
+ *       exactly as propagation.rs:27-34 fuses two hypotheses
+ *       (id, var) = fusion(inv(prior_depth), inv(new_depth), prior_variance, new_variance);
+ *       depth = inv(id) -- identical to calling tdk_fusion_dev(depth_domain=1) afterwards,
+ *       without the second pass over HBM
  *   workspace: tdk_update_depth_workspace_bytes(P,R) bytes of device scratch
  *
  * tdk_update_depth_status() copies the launch's status word back (synchronises the stream) and
@@ -89,7 +95,8 @@ int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const d
                          const double *prior_variance, const double *params, int64_t P, int64_t R,
                          int64_t H, int64_t W, double *out_depth, double *out_variance,
                          int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
-                         void *workspace, size_t workspace_bytes, void *stream);
+                         int fuse_on_success, void *workspace, size_t workspace_bytes,
+                         void *stream);
 
 /* Same, for frames that live in separate allocations (a keyframe ring kept on the device):
  * key_img_ptrs [P] and ref_img_ptrs [P*R] are HOST arrays of DEVICE image pointers. */
@@ -99,8 +106,8 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
                                 const double *prior_depth, const double *prior_variance,
                                 const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
                                 double *out_depth, double *out_variance, int64_t *out_flag,
-                                int32_t *dbg_argmin, uint64_t *out_hist, void *workspace,
-                                size_t workspace_bytes, void *stream);
+                                int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success,
+                                void *workspace, size_t workspace_bytes, void *stream);
 
 int tdk_update_depth_status(const void *workspace, void *stream);
 
@@ -115,7 +122,8 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
                           const uint64_t *age, const double *prior_depth,
                           const double *prior_variance, const double *params, int64_t P, int64_t R,
                           int64_t H, int64_t W, double *out_depth, double *out_variance,
-                          int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist);
+                          int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
+                          int fuse_on_success);
 
 /* Replaces rust_bindings.semi_dense.estimate_debug_ (src/py/semi_dense.rs:126-155): one pixel,
  * host pointers, returns the prior on failure.  u_key is (x, y).  out = {depth, variance},
@@ -129,10 +137,13 @@ int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double pri
 /* ------------------------------------------------------------------ companions
  * tdk_fusion_dev: src/semi_dense/fusion.rs:13-42 (`fusion_arrays`; not exported by the reference's
  * pyo3 module, called as tadataka.vo.semi_dense.fusion.fusion in examples/semi_dense_depth.py:41).
+ * depth_domain = 1: mu1/mu2/mu are DEPTH maps, fused in inverse depth as propagation.rs:27-34 does
+ * (inv() on the way in and out).
  * If flag != NULL only elements with flag == 0 are fused, the others keep (mu1, var1): the
  * "fuse where the update succeeded" step of examples/semi_dense_vo.py:82-88. */
 int tdk_fusion_dev(const double *mu1, const double *mu2, const double *var1, const double *var2,
-                   const int64_t *flag, int64_t n, double *mu, double *var, void *stream);
+                   const int64_t *flag, int64_t n, int depth_domain, double *mu, double *var,
+                   void *stream);
 
 /* src/semi_dense/regularization.rs:29-64 (disabled in the reference build; semantics as written):
  * per keyframe [P,H,W]. */

@@ -37,15 +37,15 @@ version = _sig("tdk_version", C.c_char_p)
 set_search_lanes = _sig("tdk_set_search_lanes", C.c_int, C.c_int)
 update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64)
 update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
-                        I64, I64, P, P, P, P, P, P, SZ, P)
+                        I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_frames_dev = _sig("tdk_update_depth_frames_dev", C.c_int, P, P, P, P, P, P, P, P, P,
-                               P, I64, I64, I64, I64, P, P, P, P, P, P, SZ, P)
+                               P, I64, I64, I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_status = _sig("tdk_update_depth_status", C.c_int, P, P)
 update_depth_host = _sig("tdk_update_depth_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
-                         I64, I64, P, P, P, P, P)
+                         I64, I64, P, P, P, P, P, C.c_int)
 estimate_debug_host = _sig("tdk_estimate_debug_host", C.c_int, P, D, D, P, P, P, P, P, P, P, I64,
                            I64, P, P, P)
-fusion_dev = _sig("tdk_fusion_dev", C.c_int, P, P, P, P, P, I64, P, P, P)
+fusion_dev = _sig("tdk_fusion_dev", C.c_int, P, P, P, P, P, I64, C.c_int, P, P, P)
 regularize_dev = _sig("tdk_regularize_dev", C.c_int, P, P, P, I64, I64, I64, P, P)
 increment_age_workspace_bytes = _sig("tdk_increment_age_workspace_bytes", SZ, I64, I64, I64)
 increment_age_dev = _sig("tdk_increment_age_dev", C.c_int, P, P, P, P, P, I64, I64, I64, P, P, SZ,

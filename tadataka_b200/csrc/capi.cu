@@ -110,7 +110,7 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
                           const uint64_t *age, const double *prior_depth, const double *prior_variance,
                           const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
                           double *out_depth, double *out_variance, int64_t *out_flag,
-                          int32_t *dbg_argmin, uint64_t *out_hist)
+                          int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success)
 {
     if (!key_imgs || !ref_imgs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
         !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
@@ -162,8 +162,8 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
         if (s.hist && rc == TDK_OK) rc = tdk_check_cuda(cudaMemsetAsync(s.hist, 0, n * 10 * 8, st), "memset hist");
         if (rc == TDK_OK)
             rc = tdk_update_depth_dev(s.key_imgs, s.key_cams, s.T_wk, s.ref_imgs, s.ref_cams, s.T_wr, s.age,
-                                      s.pd, s.pv, params, n, R, H, W, s.od, s.ov, s.of, s.dbg, s.hist, s.ws,
-                                      s.ws_bytes, st);
+                                      s.pd, s.pv, params, n, R, H, W, s.od, s.ov, s.of, s.dbg, s.hist,
+                                      fuse_on_success, s.ws, s.ws_bytes, st);
         D2H(out_depth + p0 * hw, s.od, n * hw * 8);
         D2H(out_variance + p0 * hw, s.ov, n * hw * 8);
         D2H(out_flag + p0 * hw, s.of, n * hw * 8);
@@ -223,7 +223,7 @@ int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double pri
         for (size_t i = 0; i < hw; i++) { pd[i] = prior_depth; pv[i] = prior_variance; }
         age[at] = 1;
         rc = tdk_update_depth_host(key_img, key_cam, T_wk, ref_img, ref_cam, T_wr, age, pd, pv, params, 1, 1,
-                                   H, W, od, ov, of, arg, nullptr);
+                                   H, W, od, ov, of, arg, nullptr, 0);
         if (rc == TDK_OK) {
             *out_flag = of[at];
             // py/semi_dense.rs:138-154: the prior is echoed untouched on any failure

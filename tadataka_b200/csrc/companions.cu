@@ -16,7 +16,8 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
                                                      const double *__restrict__ var1,
                                                      const double *__restrict__ var2,
                                                      const long long *__restrict__ flag, size_t n,
-                                                     double *__restrict__ mu, double *__restrict__ var)
+                                                     int depth_domain, double *__restrict__ mu,
+                                                     double *__restrict__ var)
 {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -28,7 +29,12 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
         }
         const double m2 = mu2[i], v2 = var2[i];
         const double v = v1 + v2;
-        mu[i] = (m1 * v2 + m2 * v1) / v;
+        if (depth_domain) {   // propagation.rs:27-34: fuse inverse depths, return a depth
+            const double ia = tdk::inv(m1), ib = tdk::inv(m2);
+            mu[i] = tdk::inv((ia * v2 + ib * v1) / v);
+        } else {
+            mu[i] = (m1 * v2 + m2 * v1) / v;
+        }
         var[i] = (v1 * v2) / v;
     }
 }
@@ -376,7 +382,7 @@ int check_frames(const char *who, int64_t P, int64_t H, int64_t W)
 extern "C" {
 
 int tdk_fusion_dev(const double *mu1, const double *mu2, const double *var1, const double *var2,
-                   const int64_t *flag, int64_t n, double *mu, double *var, void *stream)
+                   const int64_t *flag, int64_t n, int depth_domain, double *mu, double *var, void *stream)
 {
     if (!mu1 || !mu2 || !var1 || !var2 || !mu || !var || n < 0) {
         tdk_set_error("tdk_fusion_dev: bad argument");
@@ -386,7 +392,7 @@ int tdk_fusion_dev(const double *mu1, const double *mu2, const double *var1, con
     long long blocks = (n + TPB - 1) / TPB;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
     fusion_kernel<<<(unsigned)blocks, TPB, 0, (cudaStream_t)stream>>>(mu1, mu2, var1, var2, (const long long *)flag,
-                                                                     (size_t)n, mu, var);
+                                                                     (size_t)n, depth_domain, mu, var);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

@@ -35,7 +35,7 @@ struct UpdArgs {
     unsigned long long *hist;
     int *status;
     double vmin, vmax, geo, photo, step, min_grad;
-    int P, R, H, W, tiles_x, tiles_y;
+    int P, R, H, W, tiles_x, tiles_y, fuse;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -423,8 +423,17 @@ __global__ void __launch_bounds__(BLOCK, 2) update_depth_kernel(const UpdArgs a)
         const double idn = tdk::inv(depth);
         const int f = check_args(idn, variance, a.vmin, a.vmax);
         if (f == TDK_FLAG_SUCCESS) {
-            s_depth[owner] = tdk::inv(idn);
-            s_var[owner] = variance;
+            double nd = tdk::inv(idn), nv = variance;
+            if (a.fuse) {   // fusion.rs:3-11 in inverse depth, as propagation.rs:27-34
+                const size_t pg = map_base + (size_t)sy * W + sx;
+                const double pd = a.prior_d[pg], pv = a.prior_v[pg];
+                const double ia = tdk::inv(pd), ib = tdk::inv(nd);
+                const double vs = pv + nv;
+                nd = tdk::inv((ia * nv + ib * pv) / vs);
+                nv = (pv * nv) / vs;
+            }
+            s_depth[owner] = nd;
+            s_var[owner] = nv;
         }
         s_flag[owner] = (signed char)f;
         s_arg[owner] = arg;
@@ -473,7 +482,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
            const double *ref_cams, const double *T_wr, const uint64_t *age, const double *prior_depth,
            const double *prior_variance, const double *params, int64_t P, int64_t R, int64_t H,
            int64_t W, double *out_depth, double *out_variance, int64_t *out_flag, int32_t *dbg_argmin,
-           uint64_t *out_hist, void *workspace, size_t workspace_bytes, cudaStream_t stream)
+           uint64_t *out_hist, int fuse, void *workspace, size_t workspace_bytes, cudaStream_t stream)
 {
     if (!key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth || !prior_variance ||
         !params || !out_depth || !out_variance || !out_flag || !workspace ||
@@ -531,7 +540,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmin = 1. / (params[1] + TDK_EPS_INV);
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
-    a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y;
+    a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
     switch (g_search_lanes) {
         case 8: update_depth_kernel<8><<<(unsigned)nblocks, BLOCK, 0, stream>>>(a); break;
         case 32: update_depth_kernel<32><<<(unsigned)nblocks, BLOCK, 0, stream>>>(a); break;
@@ -567,12 +576,12 @@ int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const d
                          const uint64_t *age, const double *prior_depth, const double *prior_variance,
                          const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
                          double *out_depth, double *out_variance, int64_t *out_flag,
-                         int32_t *dbg_argmin, uint64_t *out_hist, void *workspace,
+                         int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success, void *workspace,
                          size_t workspace_bytes, void *stream)
 {
     return launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double *key_cams,
@@ -581,12 +590,12 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
                                 const double *prior_depth, const double *prior_variance,
                                 const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
                                 double *out_depth, double *out_variance, int64_t *out_flag,
-                                int32_t *dbg_argmin, uint64_t *out_hist, void *workspace,
-                                size_t workspace_bytes, void *stream)
+                                int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success,
+                                void *workspace, size_t workspace_bytes, void *stream)
 {
     return launch(nullptr, key_img_ptrs, key_cams, T_wk, nullptr, ref_img_ptrs, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int tdk_update_depth_status(const void *workspace, void *stream)

@@ -64,12 +64,14 @@ def params_array(params):
 
 
 def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_depth,
-                 prior_variance, params, debug=False, hist=False, check=True, out=None):
+                 prior_variance, params, debug=False, hist=False, check=True, out=None, fuse=False):
     """Batched update_depth (reference: src/semi_dense/semi_dense.rs:160-234).
 
     Returns (depth, variance, flag[, argmin][, hist]).  `check=True` reads the status word back
     (one stream synchronisation) and raises ValueError on age/pose/search-length errors.
     `out=(depth, variance, flag)` reuses preallocated output tensors.
+    `fuse=True` fuses each successful measurement with its prior inside the kernel (Gaussian
+    fusion in inverse depth, fusion.rs:3-11 / propagation.rs:27-34) instead of returning it raw.
     """
     _require_cuda()
     _chk(key_imgs, "key_imgs", _F64)
@@ -106,8 +108,8 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
         rc = _lib.update_depth_dev(_ptr(key_imgs), _ptr(key_cams), _ptr(T_wk), _ptr(ref_imgs),
                                    _ptr(ref_cams), _ptr(T_wr), _ptr(age), _ptr(prior_depth),
                                    _ptr(prior_variance), pa.ctypes.data_as(C.c_void_p), P, R, H, W,
-                                   _ptr(od), _ptr(ov), _ptr(of), _ptr(dbg), _ptr(hs), _ptr(ws),
-                                   ws.numel(), _stream())
+                                   _ptr(od), _ptr(ov), _ptr(of), _ptr(dbg), _ptr(hs), int(bool(fuse)),
+                                   _ptr(ws), ws.numel(), _stream())
         _lib.check(rc)
         if check:
             _lib.check(_lib.update_depth_status(_ptr(ws), _stream()))
@@ -120,7 +122,7 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
 
 
 def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, prior_depth,
-                        prior_variance, params, debug=False):
+                        prior_variance, params, debug=False, fuse=False):
     """One keyframe against a list of separately allocated reference images (a device-resident
     keyframe ring).  key_img [H,W]; ref_imgs: list of R tensors [H,W]; ref_cams [R,4];
     T_wr [R,4,4]; maps [H,W].  Returns (depth, variance, flag[, argmin]) as [H,W] tensors."""
@@ -153,7 +155,7 @@ def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, p
                                           _ptr(T_wr), _ptr(age), _ptr(prior_depth),
                                           _ptr(prior_variance), pa.ctypes.data_as(C.c_void_p), 1, R,
                                           H, W, _ptr(od), _ptr(ov), _ptr(of), _ptr(dbg), None,
-                                          _ptr(ws), ws.numel(), _stream())
+                                          int(bool(fuse)), _ptr(ws), ws.numel(), _stream())
         _lib.check(rc)
         # the pointer tables are copied with cudaMemcpyAsync from these host arrays: the status
         # read below synchronises the stream before they go out of scope
@@ -161,9 +163,10 @@ def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, p
     return (od, ov, of, dbg) if debug else (od, ov, of)
 
 
-def fusion(mu1, mu2, var1, var2, flag=None):
+def fusion(mu1, mu2, var1, var2, flag=None, depth_domain=False):
     """Gaussian fusion (reference: src/semi_dense/fusion.rs:13-42).  With `flag`, only elements
-    whose flag is SUCCESS are fused; the others keep (mu1, var1)."""
+    whose flag is SUCCESS are fused; the others keep (mu1, var1).  `depth_domain=True`: mu1/mu2 are
+    depths, fused in inverse depth and returned as a depth (propagation.rs:27-34)."""
     _require_cuda()
     shape = mu1.shape
     for t, n in ((mu1, "mu1"), (mu2, "mu2"), (var1, "var1"), (var2, "var2")):
@@ -173,7 +176,8 @@ def fusion(mu1, mu2, var1, var2, flag=None):
     with torch.cuda.device(mu1.device):
         mu, var = torch.empty_like(mu1), torch.empty_like(mu1)
         _lib.check(_lib.fusion_dev(_ptr(mu1), _ptr(mu2), _ptr(var1), _ptr(var2), _ptr(flag),
-                                   mu1.numel(), _ptr(mu), _ptr(var), _stream()))
+                                   mu1.numel(), int(bool(depth_domain)), _ptr(mu), _ptr(var),
+                                   _stream()))
     return mu, var
 
 

@@ -198,11 +198,50 @@ def test_host_pointer_entry_point_matches_device_entry_point():
     rc = _lib.update_depth_host(p(b["key_img"]), p(b["key_cam"]), p(b["T_wk"]), p(b["ref_imgs"]),
                                 p(b["ref_cams"]), p(b["T_wr"]), p(b["age"]), p(b["prior_depth"]),
                                 p(b["prior_variance"]), p(b["params"]), P, R, H, W, p(od), p(ov),
-                                p(of), p(am), p(hist))
+                                p(of), p(am), p(hist), 0)
     _lib.check(rc)
     orc = _oracle(b)
     assert_parity([od, ov, of, am], orc)
     assert [int(x) for x in hist.sum(0)] == [int((orc[2] == -k).sum()) for k in range(10)]
+
+
+def _fuse_reference(b, orc):
+    """prior (+) oracle measurement where SUCCESS, composed from IEEE numpy ops in the order of
+    propagation.rs:27-34 / fusion.rs:3-11."""
+    od, ov, of = orc[:3]
+    eps = np.finfo(np.float64).eps
+    pd, pv = b["prior_depth"], b["prior_variance"]
+    with np.errstate(all="ignore"):
+        ia, ib = 1. / (pd + eps), 1. / (od + eps)
+        vs = pv + ov
+        fd = 1. / ((ia * ov + ib * pv) / vs + eps)
+        fv = (pv * ov) / vs
+    ok = of == 0
+    return np.where(ok, fd, od), np.where(ok, fv, ov)
+
+
+def test_fused_update_equals_update_then_fusion():
+    """fuse_on_success=1 (one kernel) == update_depth + tdk_fusion_dev(depth_domain) (two kernels)
+    == the oracle's measurement fused with the prior."""
+    from tadataka_b200 import device
+    b = scene.stack_keyframes([scene.make_keyframe(2100 + i, R=4, H=240, W=320, cam=scene.CAM_VGA / 2)
+                               for i in range(3)])
+    orc = _oracle(b)
+    want_d, want_v = _fuse_reference(b, orc)
+    fused = _gpu(b, fuse=True)
+    assert np.array_equal(fused[2], orc[2]) and np.array_equal(fused[3], orc[3])
+    assert np.array_equal(fused[0], want_d) and np.array_equal(fused[1], want_v)
+    t = _dev(b)
+    d, v, f = device.update_depth(t["key_img"], t["key_cam"], t["T_wk"], t["ref_imgs"], t["ref_cams"],
+                                  t["T_wr"], t["age"], t["prior_depth"], t["prior_variance"], b["params"])
+    d2, v2 = device.fusion(t["prior_depth"], d, t["prior_variance"], v, flag=f, depth_domain=True)
+    # where not SUCCESS the two-kernel form keeps (mu1, var1) = the prior; update_depth itself stores
+    # inv(inv(prior)) for failed estimates, so compare on SUCCESS pixels and on the flags
+    ok = orc[2] == 0
+    assert np.array_equal(d2.cpu().numpy()[ok], want_d[ok])
+    assert np.array_equal(v2.cpu().numpy()[ok], want_v[ok])
+    # fusing shrinks the variance
+    assert np.all(want_v[ok] <= b["prior_variance"][ok])
 
 
 def test_newtsukuba_golden_pair():
