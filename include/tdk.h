@@ -111,6 +111,36 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
 
 int tdk_update_depth_status(const void *workspace, void *stream);
 
+/* No counterpart in the reference.  tdk_update_depth_dev needs a workspace the caller has to
+ * allocate; some callers cannot: a tracking loop that must not hit cudaMalloc's device-wide
+ * synchronisation (or its failure) once it is running, or a host application that gave this
+ * library no memory budget of its own and only passes in the buffers it owns.  This variant keeps
+ * the scratch (status words and per-pair constants, TDK_STATIC_SCRATCH_BYTES bytes) in a static
+ * device array inside the library and calls no cudaMalloc / cudaFree or any other allocating routine.
+ *   - limit: P * R <= TDK_STATIC_MAX_PAIRS keyframe/reference pairs per call; larger batches are
+ *     refused with TDK_ERR_INVALID and a message naming the limit;
+ *   - arguments as tdk_update_depth_dev (contiguous [P,H,W] / [P,R,H,W] device arrays; inputs and
+ *     outputs still belong to the caller), without the workspace;
+ *   - wait_and_check != 0: synchronise `stream` and return TDK_ERR_AGE / _SINGULAR / _SEARCH_LEN as
+ *     tdk_update_depth_status would; 0: enqueue only, errors of that kind go unreported;
+ *   - the first call on each device looks up the device address of the array
+ *     (cudaGetSymbolAddress, once per device, with that device current); make that first call
+ *     outside any stream capture;
+ *   - all calls on a device share the one array: the status words are cleared at the start of every
+ *     call, the rest is overwritten, but two calls whose kernels can overlap on the GPU (different
+ *     streams, no ordering between them) race on it -- order them, or use tdk_update_depth_dev with
+ *     separate workspaces. */
+#define TDK_STATIC_MAX_PAIRS 64
+#define TDK_STATIC_SCRATCH_BYTES 32768
+int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, const double *T_wk,
+                                const double *ref_imgs, const double *ref_cams, const double *T_wr,
+                                const uint64_t *age, const double *prior_depth,
+                                const double *prior_variance, const double *params, int64_t P,
+                                int64_t R, int64_t H, int64_t W, double *out_depth,
+                                double *out_variance, int64_t *out_flag, int32_t *dbg_argmin,
+                                uint64_t *out_hist, int fuse_on_success, int wait_and_check,
+                                void *stream);
+
 /* Tuning knob with no counterpart in the reference: how many lanes (8, 16 or 32) cooperate on
  * one pixel's epipolar search.  Results do not depend on it.  Default 16. */
 int tdk_set_search_lanes(int lanes);

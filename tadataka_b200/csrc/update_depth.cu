@@ -16,6 +16,8 @@
 // Results are staged in shared memory and written once, coalesced.
 #include <math.h>
 
+#include <mutex>
+
 #include "tdk_common.cuh"
 
 namespace {
@@ -552,6 +554,45 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Built-in scratch for tdk_update_depth_static_dev: the same bytes tdk_update_depth_dev expects in
+// its caller-provided workspace (status words, per-keyframe and per-pair constants), for batches
+// of at most TDK_STATIC_MAX_PAIRS keyframe/reference pairs.  Every device that loads this library
+// carries one copy of the array until the process exits.
+static __device__ __align__(256) unsigned char g_static_scratch[TDK_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+std::mutex g_static_mutex;
+void *g_static_scratch_addr[64] = {};   // per device ordinal; filled on the first call there
+
+// Host code cannot hand `g_static_scratch` to a kernel: on the host that name only identifies the
+// symbol to the runtime.  The address the device sees is asked for once per device, with that
+// device current, and cached.
+int static_scratch_address(void **out)
+{
+    int dev = -1;
+    TDK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        tdk_set_error("tdk_update_depth_static_dev: device ordinal %d not supported", dev);
+        return TDK_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_scratch_addr[dev]) {
+        void *addr = nullptr;
+        TDK_CUDA(cudaGetSymbolAddress(&addr, g_static_scratch));
+        if (!addr) {
+            tdk_set_error("tdk_update_depth_static_dev: cudaGetSymbolAddress returned a null address");
+            return TDK_ERR_CUDA;
+        }
+        g_static_scratch_addr[dev] = addr;
+    }
+    *out = g_static_scratch_addr[dev];
+    return TDK_OK;
+}
+
+}  // namespace
+
 extern "C" {
 
 size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R)
@@ -612,6 +653,35 @@ int tdk_update_depth_status(const void *workspace, void *stream)
         return TDK_ERR_SEARCH_LEN;
     }
     return TDK_OK;
+}
+
+int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, const double *T_wk,
+                                const double *ref_imgs, const double *ref_cams, const double *T_wr,
+                                const uint64_t *age, const double *prior_depth,
+                                const double *prior_variance, const double *params, int64_t P, int64_t R,
+                                int64_t H, int64_t W, double *out_depth, double *out_variance,
+                                int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
+                                int fuse_on_success, int wait_and_check, void *stream)
+{
+    if (P <= 0 || R <= 0 || P * R > TDK_STATIC_MAX_PAIRS ||
+        ws_layout(P, R).total > (size_t)TDK_STATIC_SCRATCH_BYTES) {
+        tdk_set_error("tdk_update_depth_static_dev: P*R = %lld x %lld exceeds the built-in scratch; this entry "
+                      "point takes at most %d keyframe/reference pairs per call (use tdk_update_depth_dev "
+                      "with a caller-owned workspace for larger batches)",
+                      (long long)P, (long long)R, TDK_STATIC_MAX_PAIRS);
+        return TDK_ERR_INVALID;
+    }
+    void *scratch = nullptr;
+    int rc = static_scratch_address(&scratch);
+    if (rc != TDK_OK) return rc;
+    // launch() zeroes the status words at the head of the scratch on `stream` before the kernels run,
+    // so nothing a previous call left behind is read; everything else in it is rewritten by
+    // pair_setup_kernel.
+    rc = launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age, prior_depth,
+                prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag, dbg_argmin, out_hist,
+                fuse_on_success, scratch, (size_t)TDK_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
+    if (rc != TDK_OK || !wait_and_check) return rc;
+    return tdk_update_depth_status(scratch, stream);
 }
 
 }  // extern "C"
