@@ -50,7 +50,7 @@ def parse():
     ap.add_argument("--distinct", type=int, default=8, help="distinct rendered scenes per GPU")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--lanes", type=int, default=0, help="search lanes override (8/16/32)")
+    ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (0 two kernels, 1 one kernel)")
     return ap.parse_args()
 
 
@@ -233,8 +233,8 @@ def run_b200(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    if args.lanes:
-        _lib.check(_lib.set_search_lanes(args.lanes))
+    if args.plan >= 0:
+        _lib.check(_lib.set_kernel_plan(args.plan))
 
     B = args.keyframes
     b = make_workload(rank, B, args.distinct)
@@ -261,7 +261,7 @@ def run_b200(args, rank, world, local_rank):
         step()
     torch.cuda.synchronize()
     # status of the warm-up launches (age / pose / search-length errors would show here)
-    ws = device.workspace(_lib.update_depth_workspace_bytes(B, R), dev, "update_depth")
+    ws = device.workspace(_lib.update_depth_workspace_bytes(B, R, H, W), dev, "update_depth")
     _lib.check(_lib.update_depth_status(C.c_void_p(ws.data_ptr()),
                                         C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
@@ -359,7 +359,7 @@ def run_b200(args, rank, world, local_rank):
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak, "peak_source": peak_src,
             "traffic": None if traffic_px is None else traffic_px * px_step,
-            "kernel": "update_depth_kernel (step time incl. the ~us pair_setup_kernel)",
+            "kernel": "update_depth sieve_kernel + search_kernel (step time, incl. the ~us pair_setup_kernel)",
             "algorithmic_bytes_per_px": ALGO_BYTES_PER_PX,
         },
         "clocks": sampler.result(),
@@ -367,7 +367,7 @@ def run_b200(args, rank, world, local_rank):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": 1e3 * e2e_s / e2e_steps,
                 "api": "tdk_update_depth_host (pinned host buffers, fuse_on_success=1)"},
-        "gpu_launches": 2 * args.steps,
+        "gpu_launches": 3 * args.steps,
     }
     if world == 1 and not args.no_cpu_baseline:
         import oracle as ora

@@ -82,12 +82,13 @@ const char *tdk_version(void);
  *       (id, var) = fusion(inv(prior_depth), inv(new_depth), prior_variance, new_variance);
  *       depth = inv(id) -- identical to calling tdk_fusion_dev(depth_domain=1) afterwards,
  *       without the second pass over HBM
- *   workspace: tdk_update_depth_workspace_bytes(P,R) bytes of device scratch
+ *   workspace: tdk_update_depth_workspace_bytes(P,R,H,W) bytes of device scratch (status words,
+ *       per-pair constants, and one u32 queue slot per pixel for the pixels that reach the search)
  *
  * tdk_update_depth_status() copies the launch's status word back (synchronises the stream) and
  * returns TDK_OK / TDK_ERR_AGE / TDK_ERR_SINGULAR / TDK_ERR_SEARCH_LEN.
  */
-size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R);
+size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R, int64_t H, int64_t W);
 
 int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const double *T_wk,
                          const double *ref_imgs, const double *ref_cams, const double *T_wr,
@@ -141,9 +142,11 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 uint64_t *out_hist, int fuse_on_success, int wait_and_check,
                                 void *stream);
 
-/* Tuning knob with no counterpart in the reference: how many lanes (8, 16 or 32) cooperate on
- * one pixel's epipolar search.  Results do not depend on it.  Default 16. */
-int tdk_set_search_lanes(int lanes);
+/* Tuning knob with no counterpart in the reference: how update_depth is mapped onto kernels.
+ * 0 (default) = two kernels: a sieve over all pixels that queues the survivors of the gradient test
+ * in the workspace, then a search kernel over 256 queued pixels per CTA; 1 = one kernel, each CTA
+ * compacts and searches its own 64x4 tile.  Results do not depend on it. */
+int tdk_set_kernel_plan(int plan);
 
 /* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,
  * checks the status.  Host buffers may be pageable or pinned. */

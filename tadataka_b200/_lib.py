@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtdk_b200.so")
+# TDK_B200_LIB: development override (an experimental build of the same sources)
+LIB_PATH = os.environ.get("TDK_B200_LIB") or os.path.join(_HERE, "libtdk_b200.so")
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_AGE, ERR_SINGULAR, ERR_WORKSPACE, ERR_SEARCH_LEN, ERR_RANGE = \
@@ -34,8 +35,8 @@ def _sig(name, restype, *argtypes):
 
 last_error = _sig("tdk_last_error", C.c_char_p)
 version = _sig("tdk_version", C.c_char_p)
-set_search_lanes = _sig("tdk_set_search_lanes", C.c_int, C.c_int)
-update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64)
+set_kernel_plan = _sig("tdk_set_kernel_plan", C.c_int, C.c_int)
+update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64, I64, I64)
 update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
                         I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_frames_dev = _sig("tdk_update_depth_frames_dev", C.c_int, P, P, P, P, P, P, P, P, P,
@@ -65,7 +66,7 @@ calc_depth0_dev = _sig("tdk_calc_depth0_dev", C.c_int, P, P, P, I64, P, P)
 
 # every symbol include/tdk.h declares (tests check the header against this list and the .so)
 EXPORTS = [
-    "tdk_last_error", "tdk_version", "tdk_set_search_lanes", "tdk_update_depth_workspace_bytes",
+    "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
     "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_status",
     "tdk_update_depth_static_dev",
     "tdk_update_depth_host", "tdk_estimate_debug_host", "tdk_fusion_dev", "tdk_regularize_dev",

@@ -33,21 +33,23 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, extra_flags=(), out=None):
+    """extra_flags / out: development variants (e.g. -DTDK_MIN_CTAS=4 -> another .so name)."""
+    if out is None and not force and not needs_build():
         return LIB
     env = dict(os.environ)
     # the image exports CC/CXX=/opt/gcc/..., nvcc wants the system host compiler
     cmd = [_nvcc(), "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS
     if verbose:
         cmd += ["-Xptxas", "-v"]
-    cmd += ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd += list(extra_flags)
+    cmd += ["-o", out or LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed building libtdk_b200.so")
-    return LIB
+    return out or LIB
 
 
 if __name__ == "__main__":

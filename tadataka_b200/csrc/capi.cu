@@ -73,8 +73,9 @@ struct Slot {
     size_t ws_bytes;
 };
 
-size_t carve_slot(char *base, size_t off, int64_t C, int64_t R, size_t hw, bool dbg, bool hist, Slot *s)
+size_t carve_slot(char *base, size_t off, int64_t C, int64_t R, int64_t H, int64_t W, bool dbg, bool hist, Slot *s)
 {
+    const size_t hw = (size_t)H * W;
     auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += up256(bytes); return p; };
     Slot t;
     t.key_imgs = (double *)take(C * hw * 8);
@@ -91,7 +92,7 @@ size_t carve_slot(char *base, size_t off, int64_t C, int64_t R, size_t hw, bool 
     t.of = (int64_t *)take(C * hw * 8);
     t.dbg = dbg ? (int32_t *)take(C * hw * 4) : nullptr;
     t.hist = hist ? (uint64_t *)take(C * 10 * 8) : nullptr;
-    t.ws_bytes = tdk_update_depth_workspace_bytes(C, R);
+    t.ws_bytes = tdk_update_depth_workspace_bytes(C, R, H, W);
     t.ws = take(t.ws_bytes);
     if (s) *s = t;
     return off;
@@ -129,13 +130,13 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
     if (C < 1) C = 1;
     if (C > P) C = P;
     const int nslots = (int)((P + C - 1) / C < NSTREAM ? (P + C - 1) / C : NSTREAM);
-    const size_t slot_bytes = carve_slot(nullptr, 0, C, R, hw, dbg_argmin != nullptr, out_hist != nullptr, nullptr);
+    const size_t slot_bytes = carve_slot(nullptr, 0, C, R, H, W, dbg_argmin != nullptr, out_hist != nullptr, nullptr);
     Arena *ar = nullptr;
     int rc = arena_get(slot_bytes * nslots, &ar);
     if (rc != TDK_OK) return rc;
     Slot slots[NSTREAM];
     for (int i = 0; i < nslots; i++)
-        carve_slot((char *)ar->base, slot_bytes * i, C, R, hw, dbg_argmin != nullptr, out_hist != nullptr, &slots[i]);
+        carve_slot((char *)ar->base, slot_bytes * i, C, R, H, W, dbg_argmin != nullptr, out_hist != nullptr, &slots[i]);
 
     const int64_t nchunks = (P + C - 1) / C;
     int(*st_host)[TDK_ST_WORDS] = nullptr;

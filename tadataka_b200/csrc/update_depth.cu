@@ -1,19 +1,15 @@
 // update_depth: per-pixel epipolar search + inverse-depth update, batched over keyframes.
 // Replaces src/semi_dense/semi_dense.rs:91-234 of the reference (see include/tdk.h).
 //
-// One launch = pair_setup_kernel (P*R threads: the per-pair constants the reference recomputes
-// for every pixel) + update_depth_kernel.  A CTA owns a 64x4 pixel tile of one keyframe and runs
-// three phases over it:
-//   A  one thread per pixel : prior checks, epipolar geometry, 5 key samples, gradient test,
-//                             reference-line end tests.  ~85-98 % of pixels finish here.
-//   B  G lanes per survivor : bilinear samples along the reference epipolar line, the
-//                             normalised 5-sample SSD for every window, shuffle argmin
-//                             (first minimum wins, as intensities.rs:24 `e < min_error`).
-//   C  one thread per survivor: triangulation, alpha / geometric / photometric variance,
-//                             final hypothesis check.
-// Survivors are compacted into a shared-memory queue between A and B, so no lane idles on a
-// finished pixel during the search, and no global scratch is needed for the queue.
-// Results are staged in shared memory and written once, coalesced.
+// pair_setup_kernel computes, once per (keyframe, reference), what the reference recomputes for
+// every pixel.  The per-pixel pipeline is cut into four phases (A1 sieve, A2 line set-up, B search,
+// C triangulation + variance; see the block comment further down) and arranged in two plans:
+//   two kernels (default): sieve_kernel runs A1 on every pixel (~85-98 % of pixels finish there) and
+//       appends the survivors to a per-keyframe queue in the workspace; search_kernel takes 256
+//       queued pixels per CTA, so A2 / B / C run with every thread of the CTA busy;
+//   one kernel: a CTA owns a 64x4 tile, compacts its own candidates in shared memory and runs all
+//       phases; needs no queue (this is what the workspace-free entry point uses).
+// Both produce bit-identical results.
 #include <math.h>
 
 #include <mutex>
@@ -25,6 +21,18 @@ namespace {
 constexpr int TILE_W = 64;
 constexpr int TILE_H = 4;
 constexpr int BLOCK = TILE_W * TILE_H;
+#ifndef TDK_MIN_CTAS
+#define TDK_MIN_CTAS 3
+#endif
+#ifndef TDK_SAMPLE_CAP
+#define TDK_SAMPLE_CAP 2048
+#endif
+#ifndef TDK_SIEVE_MIN_CTAS
+#define TDK_SIEVE_MIN_CTAS 4
+#endif
+constexpr int MIN_CTAS = TDK_MIN_CTAS;       // resident CTAs per SM the register allocation is tuned for
+constexpr int SIEVE_MIN_CTAS = TDK_SIEVE_MIN_CTAS;
+constexpr int SAMPLE_CAP = TDK_SAMPLE_CAP;   // reference-line samples a CTA stages in shared memory per batch
 
 struct UpdArgs {
     const TdkKeyConst *keys;
@@ -36,6 +44,8 @@ struct UpdArgs {
     int *dbg;
     unsigned long long *hist;
     int *status;
+    unsigned int *cand;         // two-kernel plan: [P, H*W] candidate pixel indices
+    unsigned int *cand_count;   // two-kernel plan: [P] queue lengths
     double vmin, vmax, geo, photo, step, min_grad;
     int P, R, H, W, tiles_x, tiles_y, fuse;
 };
@@ -178,18 +188,398 @@ __device__ __forceinline__ double fold9(const double *e)
     return acc;
 }
 
-template <int G>
-__global__ void __launch_bounds__(BLOCK, 2) update_depth_kernel(const UpdArgs a)
+// =============================================================================================
+// The per-pixel pipeline, cut into phases that the kernels below arrange in two ways.
+//   A1  thread per pixel      prior checks, step ratio, 5 key samples, gradient test
+//   A2  thread per candidate  reference-line ends, direction sign, line-length / end-point tests
+//   B   whole CTA             the search: samples and windows of all the CTA's lines, laid end to end
+//   C   thread per survivor   triangulation, variances, final check, optional fusion with the prior
+// Candidate state lives in a shared-memory queue (structure of arrays, BLOCK slots).
+// =============================================================================================
+struct CtaQueue {
+    double k[5][BLOCK];                       // key intensities (A1), then the normalised key window (A2)
+    double kstep[BLOCK], g[BLOCK], grev[BLOCK], idp[BLOCK], v[BLOCK], xk[BLOCK], yk[BLOCK];
+    double xminx[BLOCK], xminy[BLOCK], ux[BLOCK], uy[BLOCK], rdx[BLOCK], rdy[BLOCK];
+    int n[BLOCK], arg[BLOCK], soff[BLOCK + 1], wsum[BLOCK / 32];
+    int px[BLOCK];                            // x | y << 16 of the pixel
+    unsigned short ref[BLOCK], owner[BLOCK];  // reference index; slot of the owning thread (one-kernel plan)
+};
+
+struct A1Result {
+    double ki[5];
+    double kstep, gf, gr, idp;
+    int r;
+};
+
+// Phase A1 for pixel (x, y) with prior (d, v) and age > 0 already known to be <= R.
+// Returns a final flag (<= 0) or 1 = candidate.  out_d is what a failed pixel stores:
+// d before check_args passes, inv(inv(d)) after (semi_dense.rs:209-225).
+__device__ __forceinline__ int phase_a1(const UpdArgs &a, const TdkKeyConst &key, int p, double xk, double yk,
+                                        uint64_t age, double d, double v, double wm1, double hm1,
+                                        double &out_d, A1Result &o)
 {
+    const int W = a.W, H = a.H;
+    out_d = d;
+    const double idp = tdk::inv(d);
+    int flag = check_args(idp, v, a.vmin, a.vmax);   // semi_dense.rs:209-214
+    if (flag != TDK_FLAG_SUCCESS) return flag;
+    const double kd = tdk::inv(idp);
+    out_d = kd;
+    const int r = a.R - (int)age;
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + r;
+
+    // step_ratio, semi_dense.rs:27-40 + depth.rs:6-15
+    const double rz = pc->T[8] * (xk * kd) + pc->T[9] * (yk * kd) + pc->T[10] * (1. * kd) + pc->T[11];
+    if (rz <= 0.) return TDK_FLAG_NEGATIVE_REF_DEPTH;
+    const double kstep = (idp / tdk::inv(rz)) * a.step;
+
+    // key_coordinates, epipolar.rs:22-36.  The sign of the key direction (semi_dense.rs:42-49) needs
+    // the reference-line ends, i.e. six more divisions; it is decided in A2, for candidates only.
+    // Flipping the sign maps sample k onto sample 4-k exactly (IEEE negation is exact), so the range
+    // test is sign independent and the gradient norm only changes its summation order: both orders
+    // are tested here.
+    double kdx = xk - pc->ex, kdy = yk - pc->ey;
+    const double knorm = sqrt(kdx * kdx + kdy * kdy);
+    if (knorm != 0.) { kdx = kdx / knorm; kdy = kdy / knorm; }
+    double kcx[5], kcy[5];
+    bool key_ok = true;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const double s = kstep * (double)(k - 2);
+        kcx[k] = (xk + s * kdx) * key.fx + key.ox;
+        kcy[k] = (yk + s * kdy) * key.fy + key.oy;
+        key_ok = key_ok && tdk::in_range(kcx[k], kcy[k], wm1, hm1);
+    }
+    if (!key_ok) return TDK_FLAG_KEY_OUT_OF_RANGE;
+#pragma unroll
+    for (int k = 0; k < 5; k++) o.ki[k] = tdk::bilinear(key.img, W, H, kcx[k], kcy[k]);
+    // gradient1d + norm, gradient.rs:28-35, semi_dense.rs:130
+    const double g0 = o.ki[1] - o.ki[0], g1 = o.ki[2] - o.ki[1], g2 = o.ki[3] - o.ki[2], g3 = o.ki[4] - o.ki[3];
+    const double q0 = g0 * g0, q1 = g1 * g1, q2 = g2 * g2, q3 = g3 * g3;
+    const double sf = q0 + q1 + q2 + q3, sr = q3 + q2 + q1 + q0;
+    const double gf = sqrt(sf);
+    const double gr = sr == sf ? gf : sqrt(sr);
+    if (gf < a.min_grad && gr < a.min_grad) return TDK_FLAG_INSUFFICIENT_GRADIENT;
+    o.kstep = kstep; o.gf = gf; o.gr = gr; o.idp = idp; o.r = r;
+    return 1;
+}
+
+__device__ __forceinline__ void queue_push(CtaQueue &Q, int slot, const A1Result &c, double v, double xk, double yk,
+                                           int x, int y, int owner)
+{
+#pragma unroll
+    for (int k = 0; k < 5; k++) Q.k[k][slot] = c.ki[k];
+    Q.kstep[slot] = c.kstep; Q.g[slot] = c.gf; Q.grev[slot] = c.gr;
+    Q.idp[slot] = c.idp; Q.v[slot] = v; Q.xk[slot] = xk; Q.yk[slot] = yk;
+    Q.px[slot] = x | (y << 16);
+    Q.ref[slot] = (unsigned short)c.r;
+    Q.owner[slot] = (unsigned short)owner;
+}
+
+// Phase A2 for queue slot q.  Returns 1 (survivor; Q.n[q] = line length) or a final flag (Q.n[q] = 0).
+__device__ __forceinline__ int phase_a2(const UpdArgs &a, CtaQueue &Q, int p, int q, double wm1, double hm1)
+{
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
+    const double *__restrict__ T = pc->T;
+    const double xk = Q.xk[q], yk = Q.yk[q];
+    const double idp = Q.idp[q], v = Q.v[q];
+    int f = 1, n = 0;
+    do {
+        // hypothesis.rs:54-61, depth.rs:25-30
+        const double lo = tdk::clampd(idp - TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
+        const double hi = tdk::clampd(idp + TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
+        const double dmin = tdk::inv(hi), dmax = tdk::inv(lo);
+        // calc_ref_ends, semi_dense.rs:51-60
+        double xminx, xminy, xmaxx, xmaxy, zz;
+        tdk::warp_point(T, xk, yk, dmin, xminx, xminy, zz);
+        tdk::warp_point(T, xk, yk, dmax, xmaxx, xmaxy, zz);
+        const double rdx = xmaxx - xminx, rdy = xmaxy - xminy;
+        // calc_key_direction, semi_dense.rs:42-49: d if ref_dir . d > 0 else -d
+        const double kdx = xk - pc->ex, kdy = yk - pc->ey;
+        const bool keep = rdx * kdx + rdy * kdy > 0.;
+        double k0 = Q.k[0][q], k1 = Q.k[1][q], k2 = Q.k[2][q], k3 = Q.k[3][q], k4 = Q.k[4][q];
+        double g = Q.g[q];
+        if (!keep) {   // the reference sampled along -d: same five values in reverse order
+            double tmp = k0; k0 = k4; k4 = tmp;
+            tmp = k1; k1 = k3; k3 = tmp;
+            g = Q.grev[q];
+        }
+        if (g < a.min_grad) { f = TDK_FLAG_INSUFFICIENT_GRADIENT; break; }
+        // ref_coordinates + check_us_ref, epipolar.rs:38-54, semi_dense.rs:62-81
+        const double L = sqrt(rdx * rdx + rdy * rdy);
+        const double ux = rdx / (L + TDK_EPS), uy = rdy / (L + TDK_EPS);
+        const double nf = L / a.step;
+        if (nf > 0.) n = nf >= 2147483647. ? 2147483647 : (int)nf;   // Rust `as usize`
+        if (n < 5) { f = TDK_FLAG_REF_EPIPOLAR_TOO_SHORT; break; }
+        const double fx0 = (xminx + (0. * a.step) * ux) * pc->rfx + pc->rox;
+        const double fy0 = (xminy + (0. * a.step) * uy) * pc->rfy + pc->roy;
+        if (!tdk::in_range(fx0, fy0, wm1, hm1)) { f = TDK_FLAG_REF_CLOSE_OUT_OF_RANGE; break; }
+        const double sl = (double)(n - 1) * a.step;
+        const double fx1 = (xminx + sl * ux) * pc->rfx + pc->rox;
+        const double fy1 = (xminy + sl * uy) * pc->rfy + pc->roy;
+        if (!tdk::in_range(fx1, fy1, wm1, hm1)) { f = TDK_FLAG_REF_FAR_OUT_OF_RANGE; break; }
+        if (n > TDK_MAX_SEARCH_SAMPLES) {
+            atomicExch(&a.status[TDK_ST_SEARCH_LEN], 1);
+            n = TDK_MAX_SEARCH_SAMPLES;
+        }
+        // normalise the key window once (intensities.rs:20 does it for every window)
+        const double kn = sqrt(k0 * k0 + k1 * k1 + k2 * k2 + k3 * k3 + k4 * k4);
+        if (kn != 0.) { k0 = k0 / kn; k1 = k1 / kn; k2 = k2 / kn; k3 = k3 / kn; k4 = k4 / kn; }
+        Q.k[0][q] = k0; Q.k[1][q] = k1; Q.k[2][q] = k2; Q.k[3][q] = k3; Q.k[4][q] = k4;
+        Q.g[q] = g;
+        Q.xminx[q] = xminx; Q.xminy[q] = xminy;
+        Q.ux[q] = ux; Q.uy[q] = uy;
+        Q.rdx[q] = rdx; Q.rdy[q] = rdy;
+    } while (false);
+    Q.n[q] = f == 1 ? n : 0;
+    return f;
+}
+
+// One reference-line sample: bilinear(ref, K_r * (x_min + (i * step) * dir))
+// (epipolar.rs:38-54, camera.rs:59-61, interpolation.rs:9-43).
+struct LineGeom {
+    const double *ref;
+    double rfx, rfy, rox, roy, xminx, xminy, ux, uy;
+};
+__device__ __forceinline__ LineGeom line_geom(const UpdArgs &a, const CtaQueue &Q, int p, int q)
+{
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
+    return LineGeom{pc->ref, pc->rfx, pc->rfy, pc->rox, pc->roy, Q.xminx[q], Q.xminy[q], Q.ux[q], Q.uy[q]};
+}
+__device__ __forceinline__ double line_sample(const LineGeom &g, int i, double step, int W, int H)
+{
+    const double s = (double)i * step;
+    const double cx = (g.xminx + s * g.ux) * g.rfx + g.rox;
+    const double cy = (g.xminy + s * g.uy) * g.rfy + g.roy;
+    return tdk::bilinear(g.ref, W, H, cx, cy);
+}
+
+// || normalize(window) - normalize(kernel) ||^2   (intensities.rs:6-29, vector.rs:4-11)
+__device__ __forceinline__ double window_error(double s0, double s1, double s2, double s3, double s4,
+                                               double k0, double k1, double k2, double k3, double k4)
+{
+    const double wn = sqrt(s0 * s0 + s1 * s1 + s2 * s2 + s3 * s3 + s4 * s4);
+    double w0 = s0, w1 = s1, w2 = s2, w3 = s3, w4 = s4;
+    if (wn != 0.) { w0 = s0 / wn; w1 = s1 / wn; w2 = s2 / wn; w3 = s3 / wn; w4 = s4 / wn; }
+    const double d0 = w0 - k0, d1 = w1 - k1, d2 = w2 - k2, d3 = w3 - k3, d4 = w4 - k4;
+    return d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
+}
+
+// Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
+// argmin is an (error, index) shuffle reduction with the lowest index winning ties.  Used for lines
+// that do not fit the staging buffer.  Returns argmin (0 if no window beat +inf, as
+// intensities.rs:16-29 does) on every lane.
+__device__ __forceinline__ int search_line_warp(const LineGeom &g, int n, double step, int W, int H,
+                                                double k0, double k1, double k2, double k3, double k4, int lane)
+{
+    const int nwin = n - 4;
+    double best_e = INFINITY;
+    int best_i = 0x7fffffff;
+    for (int base = 0; base < nwin; base += 28) {
+        const int i = base + lane;
+        const double s0 = i < n ? line_sample(g, i, step, W, H) : 0.;
+        const double s1 = __shfl_down_sync(0xffffffffu, s0, 1);
+        const double s2 = __shfl_down_sync(0xffffffffu, s0, 2);
+        const double s3 = __shfl_down_sync(0xffffffffu, s0, 3);
+        const double s4 = __shfl_down_sync(0xffffffffu, s0, 4);
+        if (lane < 28 && i < nwin) {
+            const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+            if (e < best_e) { best_e = e; best_i = i; }
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const double oe = __shfl_xor_sync(0xffffffffu, best_e, off);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, off);
+        if (oe < best_e || (oe == best_e && oi < best_i)) { best_e = oe; best_i = oi; }
+    }
+    return best_i == 0x7fffffff ? 0 : best_i;
+}
+
+// Phase B for the nq slots of the queue (whole CTA; contains __syncthreads, so every thread must
+// call it with the same nq).  Writes Q.arg[q] = argmin + 2 (intensities.rs:32-36) for live lines.
+// s_buf: SAMPLE_CAP + 4 doubles; s_qid: SAMPLE_CAP line ids.
+__device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, int nq, double *s_buf,
+                                        unsigned short *s_qid)
+{
+    const int tid = threadIdx.x, W = a.W, H = a.H;
+    {   // Q.soff = exclusive prefix sum of the line lengths
+        const int v = tid < nq ? Q.n[tid] : 0;
+        const int lane = tid & 31, wid = tid >> 5;
+        int incl = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += o;
+        }
+        if (lane == 31) Q.wsum[wid] = incl;
+        __syncthreads();
+        int woff = 0;
+#pragma unroll
+        for (int w = 0; w < BLOCK / 32; w++) woff += w < wid ? Q.wsum[w] : 0;
+        Q.soff[tid] = woff + incl - v;
+        if (tid == BLOCK - 1) Q.soff[BLOCK] = woff + incl;
+    }
+    __syncthreads();
+    int qa = 0;
+    while (qa < nq) {   // batches of lines whose samples fit the staging buffer (CTA-uniform control flow)
+        const int base = Q.soff[qa];
+        int lo = qa, hi = nq + 1;   // largest qb in (qa, nq] with soff[qb] - base <= SAMPLE_CAP
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (Q.soff[mid] - base <= SAMPLE_CAP) lo = mid; else hi = mid;
+        }
+        const int qb = lo;
+        if (qb == qa) {   // one line longer than the buffer: warp 0 searches it on its own
+            if (tid < 32) {
+                const LineGeom g = line_geom(a, Q, p, qa);
+                const int arg = search_line_warp(g, Q.n[qa], a.step, W, H, Q.k[0][qa], Q.k[1][qa], Q.k[2][qa],
+                                                 Q.k[3][qa], Q.k[4][qa], tid);
+                if (tid == 0) Q.arg[qa] = arg + 2;
+            }
+            qa += 1;
+            continue;
+        }
+        const int S = Q.soff[qb] - base;
+        // pass 0: every line of the batch labels its own stretch of the sample buffer
+        if (tid >= qa && tid < qb) {
+            const int n = Q.n[tid], o = Q.soff[tid] - base;
+            for (int i = 0; i < n; i++) s_qid[o + i] = (unsigned short)tid;
+        }
+        __syncthreads();
+        // pass 1: one sample per thread
+        for (int s = tid; s < S; s += BLOCK) {
+            const int q = s_qid[s];
+            const LineGeom g = line_geom(a, Q, p, q);
+            s_buf[s] = line_sample(g, s - (Q.soff[q] - base), a.step, W, H);
+        }
+        __syncthreads();
+        // pass 2: one window per thread; its error replaces the window's first sample once every
+        // window of the round has been read (later rounds only read later samples)
+        for (int s0 = 0; s0 < S; s0 += BLOCK) {
+            const int s = s0 + tid;
+            double e = INFINITY;
+            if (s < S) {
+                const int q = s_qid[s];
+                const int i = s - (Q.soff[q] - base);
+                if (i < Q.n[q] - 4)
+                    e = window_error(s_buf[s], s_buf[s + 1], s_buf[s + 2], s_buf[s + 3], s_buf[s + 4],
+                                     Q.k[0][q], Q.k[1][q], Q.k[2][q], Q.k[3][q], Q.k[4][q]);
+            }
+            __syncthreads();
+            if (s < S) s_buf[s] = e;
+        }
+        __syncthreads();
+        // pass 3: first minimum of each line, scanned in index order like intensities.rs:16-29
+        if (tid >= qa && tid < qb && Q.n[tid] != 0) {
+            const double *e = s_buf + (Q.soff[tid] - base);
+            const int nwin = Q.n[tid] - 4;
+            double best = INFINITY;
+            int arg = 0;
+            for (int i = 0; i < nwin; i++) {
+                const double ei = e[i];
+                if (ei < best) { best = ei; arg = i; }
+            }
+            Q.arg[tid] = arg + 2;
+        }
+        __syncthreads();
+        qa = qb;
+    }
+}
+
+// Phase C for a live queue slot q.  Returns the final flag; on SUCCESS nd / nv hold the new (or
+// fused) depth and variance.
+__device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, const TdkKeyConst &key, int p, int q,
+                                       size_t map_base, double &nd, double &nv)
+{
+    const int W = a.W, H = a.H;
+    const int arg = Q.arg[q];
+    const int sx = Q.px[q] & 0xffff, sy = Q.px[q] >> 16;
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
+    const double *__restrict__ T = pc->T;
+    const double xk = Q.xk[q], yk = Q.yk[q];
+    const double s = (double)arg * a.step;
+    const double xr = Q.xminx[q] + s * Q.ux[q];
+    const double yr = Q.xminy[q] + s * Q.uy[q];
+
+    // calc_depth0, triangulation.rs:8-36
+    const double rzy = T[8] * xk + T[9] * yk + T[10] * 1.;
+    const double r0y = T[0] * xk + T[1] * yk + T[2] * 1.;
+    const double r1y = T[4] * xk + T[5] * yk + T[6] * 1.;
+    const double tzz = T[11];
+    const bool ax0 = fabs(T[3]) > fabs(T[7]);
+    const double x1i = ax0 ? xr : yr, ti = ax0 ? T[3] : T[7], riy = ax0 ? r0y : r1y;
+    const double depth = (ti - tzz * x1i) / ((rzy * x1i - riy) + TDK_EPS);
+
+    // calc_alpha, variance.rs:55-106
+    const double rdx = Q.rdx[q], rdy = Q.rdy[q];
+    const double rn = sqrt(rdx * rdx + rdy * rdy);
+    const double dhx = rn == 0. ? rdx : rdx / rn, dhy = rn == 0. ? rdy : rdy / rn;
+    double xrefx, xrefy, zz;
+    tdk::warp_point(T, xk, yk, depth, xrefx, xrefy, zz);
+    const bool bx0 = fabs(dhx) > fabs(dhy);
+    const double xref_i = bx0 ? xrefx : xrefy, dir_i = bx0 ? dhx : dhy;
+    const double tj = bx0 ? T[3] : T[7], rjy = bx0 ? r0y : r1y;
+    const double ad = rzy * tj - rjy * tzz;
+    const double an = xref_i * tzz - tj;
+    const double alpha = dir_i * ad / (an * an);
+
+    // geo_var, variance.rs:30-53 ; Sobel at the integer pixel, border = 0
+    double gx = 0., gy = 0.;
+    if (sx > 0 && sy > 0 && sx < W - 1 && sy < H - 1) {
+        const double *c = key.img + (size_t)sy * W + sx;
+        const double m00 = __ldg(c - W - 1), m01 = __ldg(c - W), m02 = __ldg(c - W + 1);
+        const double m10 = __ldg(c - 1), m11 = __ldg(c), m12 = __ldg(c + 1);
+        const double m20 = __ldg(c + W - 1), m21 = __ldg(c + W), m22 = __ldg(c + W + 1);
+        const double ex[9] = {1. * m00, 0. * m01, -1. * m02, 2. * m10, 0. * m11, -2. * m12,
+                              1. * m20, 0. * m21, -1. * m22};
+        const double ey[9] = {1. * m00, 2. * m01, 1. * m02, 0. * m10, 0. * m11, 0. * m12,
+                              -1. * m20, -2. * m21, -1. * m22};
+        gx = fold9(ex);
+        gy = fold9(ey);
+    }
+    double lx2 = xk - pc->ptx, ly2 = yk - pc->pty;
+    const double ln = sqrt(lx2 * lx2 + ly2 * ly2);
+    if (ln != 0.) { lx2 = lx2 / ln; ly2 = ly2 / ln; }
+    const double gn = sqrt(gx * gx + gy * gy);
+    if (gn != 0.) { gx = gx / gn; gy = gy / gn; }
+    const double pp = lx2 * gx + ly2 * gy;
+    const double geo_var = pp == 0. ? 1. / TDK_EPS : 1. / (pp * pp);
+    const double photo_var = 2. / (Q.g[q] / Q.kstep[q]);
+    const double variance = (alpha * alpha) * ((a.geo * a.geo) * geo_var + (a.photo * a.photo) * photo_var);
+
+    const double idn = tdk::inv(depth);
+    const int f = check_args(idn, variance, a.vmin, a.vmax);
+    if (f == TDK_FLAG_SUCCESS) {
+        nd = tdk::inv(idn);
+        nv = variance;
+        if (a.fuse) {   // fusion.rs:3-11 in inverse depth, as propagation.rs:27-34
+            const double pd = a.prior_d[map_base + (size_t)sy * W + sx], pv = Q.v[q];
+            const double ia = tdk::inv(pd), ib = tdk::inv(nd);
+            const double vs = pv + nv;
+            nd = tdk::inv((ia * nv + ib * pv) / vs);
+            nv = (pv * nv) / vs;
+        }
+    }
+    return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// One-kernel plan: a CTA owns a 64x4 tile, compacts its own candidates and runs every phase.
+// Needs no global queue (this is what tdk_update_depth_static_dev runs), but only the tile's own
+// ~5-15 % of candidates populate phases A2/B/C.
+__global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(const UpdArgs a)
+{
+    __shared__ CtaQueue Q;
     __shared__ double s_depth[BLOCK], s_var[BLOCK];
-    __shared__ double q_xminx[BLOCK], q_xminy[BLOCK], q_ux[BLOCK], q_uy[BLOCK];
-    __shared__ double q_rdx[BLOCK], q_rdy[BLOCK], q_kstep[BLOCK], q_g[BLOCK];
-    __shared__ double q_k[5][BLOCK];
-    __shared__ int q_n[BLOCK], q_arg[BLOCK], s_arg[BLOCK];
-    __shared__ unsigned short q_pix[BLOCK], q_ref[BLOCK];
+    __shared__ int s_arg[BLOCK];
     __shared__ signed char s_flag[BLOCK];
+    __shared__ double s_xk[TILE_W], s_yk[TILE_H];    // normalised key coordinates of the tile
     __shared__ int s_nq;
     __shared__ unsigned int s_hist[10];
+    extern __shared__ double s_dyn[];                // SAMPLE_CAP + 4 samples, then SAMPLE_CAP line ids
+    double *const s_buf = s_dyn;
+    unsigned short *const s_qid = (unsigned short *)(s_dyn + SAMPLE_CAP + 4);
 
     const int tid = threadIdx.x;
     const int tiles = a.tiles_x * a.tiles_y;
@@ -203,11 +593,15 @@ __global__ void __launch_bounds__(BLOCK, 2) update_depth_kernel(const UpdArgs a)
 
     if (tid == 0) s_nq = 0;
     if (tid < 10) s_hist[tid] = 0;
+    // camera.rs:55-57: x_key depends on the column (row) only -- one division per column (row) of
+    // the tile instead of two per pixel
+    if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
+    else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
     __syncthreads();
 
-    // ------------------------------------------------------------------ phase A
-    const int x = tx * TILE_W + (tid & (TILE_W - 1));
-    const int y = ty * TILE_H + (tid / TILE_W);
+    // ---- phase A1
+    const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
+    const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
     const bool valid = x < W && y < H;
     const size_t pix = map_base + (size_t)y * W + x;
     int flag = TDK_FLAG_NOT_PROCESSED;
@@ -215,234 +609,44 @@ __global__ void __launch_bounds__(BLOCK, 2) update_depth_kernel(const UpdArgs a)
     if (valid) {
         const uint64_t age = a.age[pix];
         const double d = a.prior_d[pix], v = a.prior_v[pix];
-        double out_d = d, out_v = v;
-        do {
-            if (age == 0) break;   // semi_dense.rs:194-200
-            if (age > (uint64_t)a.R) { atomicExch(&a.status[TDK_ST_AGE], 1); break; }
-            const double idp = tdk::inv(d);
-            flag = check_args(idp, v, a.vmin, a.vmax);   // semi_dense.rs:209-214
-            if (flag != TDK_FLAG_SUCCESS) break;
-            // from here on a failure stores inv(inv(d))  (semi_dense.rs:220-225)
-            out_d = tdk::inv(idp);
-            const int r = a.R - (int)age;
-            const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + r;
-            const double *__restrict__ T = pc->T;
-
-            // hypothesis.rs:54-61, depth.rs:25-30
-            const double lo = tdk::clampd(idp - TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
-            const double hi = tdk::clampd(idp + TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
-            const double dmin = tdk::inv(hi), dmax = tdk::inv(lo);
-            const double xk = ((double)x - key.ox) / key.fx;   // camera.rs:55-57
-            const double yk = ((double)y - key.oy) / key.fy;
-
-            // step_ratio, semi_dense.rs:27-40 + depth.rs:6-15
-            const double kd = tdk::inv(idp);
-            const double rz = T[8] * (xk * kd) + T[9] * (yk * kd) + T[10] * (1. * kd) + T[11];
-            if (rz <= 0.) { flag = TDK_FLAG_NEGATIVE_REF_DEPTH; break; }
-            const double kstep = (idp / tdk::inv(rz)) * a.step;
-
-            // calc_ref_ends, semi_dense.rs:51-60
-            double xminx, xminy, xmaxx, xmaxy, zz;
-            tdk::warp_point(T, xk, yk, dmin, xminx, xminy, zz);
-            tdk::warp_point(T, xk, yk, dmax, xmaxx, xmaxy, zz);
-            const double rdx = xmaxx - xminx, rdy = xmaxy - xminy;
-
-            // calc_key_direction, semi_dense.rs:42-49 ; key_coordinates, epipolar.rs:22-36
-            double kdx = xk - pc->ex, kdy = yk - pc->ey;
-            if (!(rdx * kdx + rdy * kdy > 0.)) { kdx = -kdx; kdy = -kdy; }
-            const double knorm = sqrt(kdx * kdx + kdy * kdy);
-            if (knorm != 0.) { kdx = kdx / knorm; kdy = kdy / knorm; }
-            double ki[5], kcx[5], kcy[5];
-            bool key_ok = true;
-#pragma unroll
-            for (int k = 0; k < 5; k++) {
-                const double s = kstep * (double)(k - 2);
-                kcx[k] = (xk + s * kdx) * key.fx + key.ox;
-                kcy[k] = (yk + s * kdy) * key.fy + key.oy;
-                key_ok = key_ok && tdk::in_range(kcx[k], kcy[k], wm1, hm1);
+        double out_d = d;
+        if (age != 0) {   // semi_dense.rs:194-200
+            if (age > (uint64_t)a.R) {
+                atomicExch(&a.status[TDK_ST_AGE], 1);
+            } else {
+                A1Result c;
+                flag = phase_a1(a, key, p, s_xk[lx], s_yk[ly], age, d, v, wm1, hm1, out_d, c);
+                if (flag == 1) queue_push(Q, atomicAdd(&s_nq, 1), c, v, s_xk[lx], s_yk[ly], x, y, tid);
             }
-            if (!key_ok) { flag = TDK_FLAG_KEY_OUT_OF_RANGE; break; }
-#pragma unroll
-            for (int k = 0; k < 5; k++) ki[k] = tdk::bilinear(key.img, W, H, kcx[k], kcy[k]);
-            // gradient1d + norm, gradient.rs:28-35, semi_dense.rs:130
-            const double g0 = ki[1] - ki[0], g1 = ki[2] - ki[1], g2 = ki[3] - ki[2], g3 = ki[4] - ki[3];
-            const double g = sqrt(g0 * g0 + g1 * g1 + g2 * g2 + g3 * g3);
-            if (g < a.min_grad) { flag = TDK_FLAG_INSUFFICIENT_GRADIENT; break; }
-
-            // ref_coordinates + check_us_ref, epipolar.rs:38-54, semi_dense.rs:62-81
-            const double L = sqrt(rdx * rdx + rdy * rdy);
-            const double ux = rdx / (L + TDK_EPS), uy = rdy / (L + TDK_EPS);
-            const double nf = L / a.step;
-            int n = 0;
-            if (nf > 0.) n = nf >= 2147483647. ? 2147483647 : (int)nf;   // Rust `as usize`
-            if (n < 5) { flag = TDK_FLAG_REF_EPIPOLAR_TOO_SHORT; break; }
-            {
-                const double fx0 = (xminx + (0. * a.step) * ux) * pc->rfx + pc->rox;
-                const double fy0 = (xminy + (0. * a.step) * uy) * pc->rfy + pc->roy;
-                if (!tdk::in_range(fx0, fy0, wm1, hm1)) { flag = TDK_FLAG_REF_CLOSE_OUT_OF_RANGE; break; }
-                const double sl = (double)(n - 1) * a.step;
-                const double fx1 = (xminx + sl * ux) * pc->rfx + pc->rox;
-                const double fy1 = (xminy + sl * uy) * pc->rfy + pc->roy;
-                if (!tdk::in_range(fx1, fy1, wm1, hm1)) { flag = TDK_FLAG_REF_FAR_OUT_OF_RANGE; break; }
-            }
-            if (n > TDK_MAX_SEARCH_SAMPLES) {
-                atomicExch(&a.status[TDK_ST_SEARCH_LEN], 1);
-                n = TDK_MAX_SEARCH_SAMPLES;
-            }
-            // survivor: normalise the key window once (intensities.rs:20 does it per window)
-            const double kn = sqrt(ki[0] * ki[0] + ki[1] * ki[1] + ki[2] * ki[2] + ki[3] * ki[3] + ki[4] * ki[4]);
-            const int slot = atomicAdd(&s_nq, 1);
-#pragma unroll
-            for (int k = 0; k < 5; k++) q_k[k][slot] = kn == 0. ? ki[k] : ki[k] / kn;
-            q_xminx[slot] = xminx; q_xminy[slot] = xminy;
-            q_ux[slot] = ux; q_uy[slot] = uy;
-            q_rdx[slot] = rdx; q_rdy[slot] = rdy;
-            q_kstep[slot] = kstep; q_g[slot] = g;
-            q_n[slot] = n;
-            q_pix[slot] = (unsigned short)tid;
-            q_ref[slot] = (unsigned short)r;
-            out_v = v;
-            flag = 1;   // pending
-        } while (false);
+        }
         s_depth[tid] = out_d;
-        s_var[tid] = out_v;
+        s_var[tid] = v;
     }
     s_flag[tid] = (signed char)flag;
     __syncthreads();
 
-    // ------------------------------------------------------------------ phase B
+    // ---- phase A2
     const int nq = s_nq;
-    {
-        constexpr int NGRP = BLOCK / G;
-        const int lane = tid & (G - 1);
-        const int grp = tid / G;
-        const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << ((tid & 31) & ~(G - 1)));
-        for (int q = grp; q < nq; q += NGRP) {
-            const int n = q_n[q];
-            const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + q_ref[q];
-            const double *__restrict__ ref = pc->ref;
-            const double rfx = pc->rfx, rfy = pc->rfy, rox = pc->rox, roy = pc->roy;
-            const double xminx = q_xminx[q], xminy = q_xminy[q], ux = q_ux[q], uy = q_uy[q];
-            const double k0 = q_k[0][q], k1 = q_k[1][q], k2 = q_k[2][q], k3 = q_k[3][q], k4 = q_k[4][q];
-            const int nwin = n - 4;
-            double best_e = INFINITY;
-            int best_i = 0x7fffffff;
-            for (int base = 0; base < nwin; base += G - 4) {
-                const int i = base + lane;
-                double s0 = 0.;
-                if (i < n) {
-                    const double s = (double)i * a.step;
-                    const double cx = (xminx + s * ux) * rfx + rox;
-                    const double cy = (xminy + s * uy) * rfy + roy;
-                    s0 = tdk::bilinear(ref, W, H, cx, cy);
-                }
-                const double s1 = __shfl_down_sync(gmask, s0, 1, G);
-                const double s2 = __shfl_down_sync(gmask, s0, 2, G);
-                const double s3 = __shfl_down_sync(gmask, s0, 3, G);
-                const double s4 = __shfl_down_sync(gmask, s0, 4, G);
-                if (lane < G - 4 && i < nwin) {
-                    // intensities.rs:6-29: || normalize(window) - normalize(kernel) ||^2
-                    const double wn = sqrt(s0 * s0 + s1 * s1 + s2 * s2 + s3 * s3 + s4 * s4);
-                    double w0 = s0, w1 = s1, w2 = s2, w3 = s3, w4 = s4;
-                    if (wn != 0.) { w0 = s0 / wn; w1 = s1 / wn; w2 = s2 / wn; w3 = s3 / wn; w4 = s4 / wn; }
-                    const double d0 = w0 - k0, d1 = w1 - k1, d2 = w2 - k2, d3 = w3 - k3, d4 = w4 - k4;
-                    const double e = d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
-                    if (e < best_e) { best_e = e; best_i = i; }
-                }
-            }
-#pragma unroll
-            for (int off = G / 2; off > 0; off >>= 1) {
-                const double oe = __shfl_xor_sync(gmask, best_e, off, G);
-                const int oi = __shfl_xor_sync(gmask, best_i, off, G);
-                if (oe < best_e || (oe == best_e && oi < best_i)) { best_e = oe; best_i = oi; }
-            }
-            if (lane == 0) q_arg[q] = (best_i == 0x7fffffff ? 0 : best_i) + 2;   // intensities.rs:32-36
-        }
-    }
-    __syncthreads();
-
-    // ------------------------------------------------------------------ phase C
     if (tid < nq) {
-        const int q = tid;
-        const int owner = q_pix[q];
-        const int arg = q_arg[q];
-        const int sx = tx * TILE_W + (owner & (TILE_W - 1));
-        const int sy = ty * TILE_H + (owner / TILE_W);
-        const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + q_ref[q];
-        const double *__restrict__ T = pc->T;
-        const double xk = ((double)sx - key.ox) / key.fx;
-        const double yk = ((double)sy - key.oy) / key.fy;
-        const double s = (double)arg * a.step;
-        const double xr = q_xminx[q] + s * q_ux[q];
-        const double yr = q_xminy[q] + s * q_uy[q];
-
-        // calc_depth0, triangulation.rs:8-36
-        const double rzy = T[8] * xk + T[9] * yk + T[10] * 1.;
-        const double r0y = T[0] * xk + T[1] * yk + T[2] * 1.;
-        const double r1y = T[4] * xk + T[5] * yk + T[6] * 1.;
-        const double tzz = T[11];
-        const bool ax0 = fabs(T[3]) > fabs(T[7]);
-        const double x1i = ax0 ? xr : yr, ti = ax0 ? T[3] : T[7], riy = ax0 ? r0y : r1y;
-        const double depth = (ti - tzz * x1i) / ((rzy * x1i - riy) + TDK_EPS);
-
-        // calc_alpha, variance.rs:55-106
-        const double rdx = q_rdx[q], rdy = q_rdy[q];
-        const double rn = sqrt(rdx * rdx + rdy * rdy);
-        const double dhx = rn == 0. ? rdx : rdx / rn, dhy = rn == 0. ? rdy : rdy / rn;
-        double xrefx, xrefy, zz;
-        tdk::warp_point(T, xk, yk, depth, xrefx, xrefy, zz);
-        const bool bx0 = fabs(dhx) > fabs(dhy);
-        const double xref_i = bx0 ? xrefx : xrefy, dir_i = bx0 ? dhx : dhy;
-        const double tj = bx0 ? T[3] : T[7], rjy = bx0 ? r0y : r1y;
-        const double ad = rzy * tj - rjy * tzz;
-        const double an = xref_i * tzz - tj;
-        const double alpha = dir_i * ad / (an * an);
-
-        // geo_var, variance.rs:30-53 ; Sobel at the integer pixel, border = 0
-        double gx = 0., gy = 0.;
-        if (sx > 0 && sy > 0 && sx < W - 1 && sy < H - 1) {
-            const double *c = key.img + (size_t)sy * W + sx;
-            const double m00 = __ldg(c - W - 1), m01 = __ldg(c - W), m02 = __ldg(c - W + 1);
-            const double m10 = __ldg(c - 1), m11 = __ldg(c), m12 = __ldg(c + 1);
-            const double m20 = __ldg(c + W - 1), m21 = __ldg(c + W), m22 = __ldg(c + W + 1);
-            const double ex[9] = {1. * m00, 0. * m01, -1. * m02, 2. * m10, 0. * m11, -2. * m12,
-                                  1. * m20, 0. * m21, -1. * m22};
-            const double ey[9] = {1. * m00, 2. * m01, 1. * m02, 0. * m10, 0. * m11, 0. * m12,
-                                  -1. * m20, -2. * m21, -1. * m22};
-            gx = fold9(ex);
-            gy = fold9(ey);
-        }
-        double lx = xk - pc->ptx, ly = yk - pc->pty;
-        const double ln = sqrt(lx * lx + ly * ly);
-        if (ln != 0.) { lx = lx / ln; ly = ly / ln; }
-        const double gn = sqrt(gx * gx + gy * gy);
-        if (gn != 0.) { gx = gx / gn; gy = gy / gn; }
-        const double pp = lx * gx + ly * gy;
-        const double geo_var = pp == 0. ? 1. / TDK_EPS : 1. / (pp * pp);
-        const double photo_var = 2. / (q_g[q] / q_kstep[q]);
-        const double variance = (alpha * alpha) * ((a.geo * a.geo) * geo_var + (a.photo * a.photo) * photo_var);
-
-        const double idn = tdk::inv(depth);
-        const int f = check_args(idn, variance, a.vmin, a.vmax);
-        if (f == TDK_FLAG_SUCCESS) {
-            double nd = tdk::inv(idn), nv = variance;
-            if (a.fuse) {   // fusion.rs:3-11 in inverse depth, as propagation.rs:27-34
-                const size_t pg = map_base + (size_t)sy * W + sx;
-                const double pd = a.prior_d[pg], pv = a.prior_v[pg];
-                const double ia = tdk::inv(pd), ib = tdk::inv(nd);
-                const double vs = pv + nv;
-                nd = tdk::inv((ia * nv + ib * pv) / vs);
-                nv = (pv * nv) / vs;
-            }
-            s_depth[owner] = nd;
-            s_var[owner] = nv;
-        }
-        s_flag[owner] = (signed char)f;
-        s_arg[owner] = arg;
+        const int f = phase_a2(a, Q, p, tid, wm1, hm1);
+        if (f != 1) s_flag[Q.owner[tid]] = (signed char)f;
     }
     __syncthreads();
 
-    // ------------------------------------------------------------------ store
+    phase_b(a, Q, p, nq, s_buf, s_qid);
+
+    // ---- phase C
+    if (tid < nq && Q.n[tid] != 0) {
+        double nd, nv;
+        const int f = phase_c(a, Q, key, p, tid, map_base, nd, nv);
+        const int owner = Q.owner[tid];
+        if (f == TDK_FLAG_SUCCESS) { s_depth[owner] = nd; s_var[owner] = nv; }
+        s_flag[owner] = (signed char)f;
+        s_arg[owner] = Q.arg[tid];
+    }
+    __syncthreads();
+
+    // ---- store
     if (valid) {
         const int f = s_flag[tid];
         a.out_d[pix] = s_depth[tid];
@@ -458,13 +662,134 @@ __global__ void __launch_bounds__(BLOCK, 2) update_depth_kernel(const UpdArgs a)
 }
 
 // ---------------------------------------------------------------------------------------------
+// Two-kernel plan.  sieve_kernel runs phase A1 on every pixel, stores the result of every pixel
+// that is finished (and the provisional prior for candidates) and appends the candidates of its
+// tile to the keyframe's queue in global memory.  search_kernel then takes 256 candidates of one
+// keyframe per CTA, so phases A2 / B / C run with every thread busy.
+__global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kernel(const UpdArgs a)
+{
+    __shared__ double s_xk[TILE_W], s_yk[TILE_H];
+    __shared__ unsigned int s_hist[10];
+    __shared__ int s_cnt, s_base;
+
+    const int tid = threadIdx.x;
+    const int tiles = a.tiles_x * a.tiles_y;
+    const int p = blockIdx.x / tiles;
+    const int t = blockIdx.x - p * tiles;
+    const int ty = t / a.tiles_x, tx = t - ty * a.tiles_x;
+    const int W = a.W, H = a.H;
+    const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
+    const TdkKeyConst key = a.keys[p];
+    const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
+
+    if (tid == 0) s_cnt = 0;
+    if (tid < 10) s_hist[tid] = 0;
+    if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
+    else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
+    __syncthreads();
+
+    const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
+    const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
+    const bool valid = x < W && y < H;
+    const size_t pix = map_base + (size_t)y * W + x;
+    int flag = TDK_FLAG_NOT_PROCESSED, slot = -1;
+    if (valid) {
+        const uint64_t age = a.age[pix];
+        const double d = a.prior_d[pix], v = a.prior_v[pix];
+        double out_d = d;
+        if (age != 0) {
+            if (age > (uint64_t)a.R) {
+                atomicExch(&a.status[TDK_ST_AGE], 1);
+            } else {
+                A1Result c;
+                flag = phase_a1(a, key, p, s_xk[lx], s_yk[ly], age, d, v, wm1, hm1, out_d, c);
+                if (flag == 1) slot = atomicAdd(&s_cnt, 1);
+            }
+        }
+        // candidates get the values a failed estimate keeps; search_kernel overwrites them on success
+        a.out_d[pix] = out_d;
+        a.out_v[pix] = v;
+        a.out_f[pix] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
+        if (a.dbg) a.dbg[pix] = -1;
+        if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
+    }
+    __syncthreads();
+    if (tid == 0 && s_cnt > 0) s_base = (int)atomicAdd(a.cand_count + p, (unsigned int)s_cnt);
+    __syncthreads();
+    if (slot >= 0) a.cand[map_base + (size_t)(s_base + slot)] = (unsigned int)(y * W + x);
+    if (a.hist && tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+}
+
+__global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(const UpdArgs a)
+{
+    __shared__ CtaQueue Q;
+    __shared__ unsigned int s_hist[10];
+    extern __shared__ double s_dyn[];
+    double *const s_buf = s_dyn;
+    unsigned short *const s_qid = (unsigned short *)(s_dyn + SAMPLE_CAP + 4);
+
+    const int tid = threadIdx.x;
+    const int chunks = a.tiles_x * a.tiles_y;   // ceil(H*W / BLOCK)
+    const int p = blockIdx.x / chunks;
+    const int chunk = blockIdx.x - p * chunks;
+    const int total = (int)a.cand_count[p];
+    const int first = chunk * BLOCK;
+    if (first >= total) return;
+    const int nq = min(BLOCK, total - first);
+    const int W = a.W, H = a.H;
+    const size_t map_base = (size_t)p * H * W;
+    const TdkKeyConst key = a.keys[p];
+    const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
+    if (tid < 10) s_hist[tid] = 0;
+
+    // ---- phase A1 again for this CTA's candidates (same arithmetic, so they all pass again), then A2
+    int flag = 1;
+    size_t pix = 0;
+    double fail_d = 0.;
+    if (tid < nq) {
+        const unsigned int li = a.cand[map_base + first + tid];
+        const int y = (int)(li / (unsigned int)W), x = (int)(li - (unsigned int)y * W);
+        pix = map_base + li;
+        const uint64_t age = a.age[pix];
+        const double d = a.prior_d[pix], v = a.prior_v[pix];
+        const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
+        A1Result c;
+        phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
+        queue_push(Q, tid, c, v, xk, yk, x, y, tid);
+        flag = phase_a2(a, Q, p, tid, wm1, hm1);
+    }
+    __syncthreads();
+
+    phase_b(a, Q, p, nq, s_buf, s_qid);
+
+    // ---- phase C and the scattered store of this CTA's candidates
+    if (tid < nq) {
+        int arg = -1;
+        if (flag == 1) {
+            double nd, nv;
+            flag = phase_c(a, Q, key, p, tid, map_base, nd, nv);
+            arg = Q.arg[tid];
+            if (flag == TDK_FLAG_SUCCESS) { a.out_d[pix] = nd; a.out_v[pix] = nv; }
+        }
+        if (flag != TDK_FLAG_SUCCESS) a.out_f[pix] = (long long)flag;
+        if (a.dbg) a.dbg[pix] = arg;
+        if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+    }
+    if (a.hist) {
+        __syncthreads();
+        if (tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t status, keys, pairs, key_ptrs, ref_ptrs, total;
+    size_t status, keys, pairs, key_ptrs, ref_ptrs, total_tile, cand_count, cand, total;
 };
 
-WsLayout ws_layout(int64_t P, int64_t R)
+// total_tile: what the one-kernel plan needs; total: plus the candidate queues of the two-kernel plan
+WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W)
 {
     WsLayout l;
     size_t off = 0;
@@ -473,18 +798,24 @@ WsLayout ws_layout(int64_t P, int64_t R)
     l.pairs = off; off = align_up(off + (size_t)P * R * sizeof(TdkPairConst), 256);
     l.key_ptrs = off; off = align_up(off + (size_t)P * sizeof(void *), 256);
     l.ref_ptrs = off; off = align_up(off + (size_t)P * R * sizeof(void *), 256);
+    l.total_tile = off;
+    l.cand_count = off; off = align_up(off + (size_t)P * sizeof(unsigned int), 256);
+    l.cand = off; off = align_up(off + (size_t)P * H * W * sizeof(unsigned int), 256);
     l.total = off;
     return l;
 }
 
-int g_search_lanes = 16;
+enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1 };
+int g_plan = PLAN_TWO_KERNELS;
+constexpr size_t FLAT_DYN_SMEM = (SAMPLE_CAP + 4) * sizeof(double) + SAMPLE_CAP * sizeof(unsigned short);
 
 int launch(const double *key_imgs, const double *const *key_ptrs_host, const double *key_cams,
            const double *T_wk, const double *ref_imgs, const double *const *ref_ptrs_host,
            const double *ref_cams, const double *T_wr, const uint64_t *age, const double *prior_depth,
            const double *prior_variance, const double *params, int64_t P, int64_t R, int64_t H,
            int64_t W, double *out_depth, double *out_variance, int64_t *out_flag, int32_t *dbg_argmin,
-           uint64_t *out_hist, int fuse, void *workspace, size_t workspace_bytes, cudaStream_t stream)
+           uint64_t *out_hist, int fuse, int plan, void *workspace, size_t workspace_bytes,
+           cudaStream_t stream)
 {
     if (!key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth || !prior_variance ||
         !params || !out_depth || !out_variance || !out_flag || !workspace ||
@@ -501,9 +832,10 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         tdk_set_error("tdk_update_depth: ref_step_size must be > 0 (got %g)", params[4]);
         return TDK_ERR_INVALID;
     }
-    const WsLayout l = ws_layout(P, R);
-    if (workspace_bytes < l.total) {
-        tdk_set_error("tdk_update_depth: workspace %zu < required %zu", workspace_bytes, l.total);
+    const WsLayout l = ws_layout(P, R, H, W);
+    const size_t need = plan == PLAN_ONE_KERNEL ? l.total_tile : l.total;
+    if (workspace_bytes < need) {
+        tdk_set_error("tdk_update_depth: workspace %zu < required %zu", workspace_bytes, need);
         return TDK_ERR_WORKSPACE;
     }
     const int tiles_x = (int)((W + TILE_W - 1) / TILE_W), tiles_y = (int)((H + TILE_H - 1) / TILE_H);
@@ -543,10 +875,26 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
-    switch (g_search_lanes) {
-        case 8: update_depth_kernel<8><<<(unsigned)nblocks, BLOCK, 0, stream>>>(a); break;
-        case 32: update_depth_kernel<32><<<(unsigned)nblocks, BLOCK, 0, stream>>>(a); break;
-        default: update_depth_kernel<16><<<(unsigned)nblocks, BLOCK, 0, stream>>>(a); break;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    TDK_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        TDK_CUDA(cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)FLAT_DYN_SMEM));
+        TDK_CUDA(cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)FLAT_DYN_SMEM));
+        attr_set[dev] = true;
+    }
+    if (plan == PLAN_ONE_KERNEL) {
+        a.cand = nullptr; a.cand_count = nullptr;
+        update_depth_tile_kernel<<<(unsigned)nblocks, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+    } else {
+        a.cand_count = (unsigned int *)(ws + l.cand_count);
+        a.cand = (unsigned int *)(ws + l.cand);
+        TDK_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)P * sizeof(unsigned int), stream));
+        update_depth_sieve_kernel<<<(unsigned)nblocks, BLOCK, 0, stream>>>(a);
+        TDK_CUDA(cudaGetLastError());
+        update_depth_search_kernel<<<(unsigned)nblocks, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
@@ -595,20 +943,20 @@ int static_scratch_address(void **out)
 
 extern "C" {
 
-size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R)
+size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R, int64_t H, int64_t W)
 {
-    if (P <= 0 || R <= 0) return 0;
-    return ws_layout(P, R).total;
+    if (P <= 0 || R <= 0 || H <= 0 || W <= 0) return 0;
+    return ws_layout(P, R, H, W).total;
 }
 
-// tuning knob (not part of the reference surface): lanes that cooperate on one epipolar line
-int tdk_set_search_lanes(int lanes)
+// tuning knob (not part of the reference surface): how update_depth is mapped onto kernels
+int tdk_set_kernel_plan(int plan)
 {
-    if (lanes != 8 && lanes != 16 && lanes != 32) {
-        tdk_set_error("tdk_set_search_lanes: %d not in {8,16,32}", lanes);
+    if (plan != PLAN_TWO_KERNELS && plan != PLAN_ONE_KERNEL) {
+        tdk_set_error("tdk_set_kernel_plan: %d not in {0,1}", plan);
         return TDK_ERR_INVALID;
     }
-    g_search_lanes = lanes;
+    g_plan = plan;
     return TDK_OK;
 }
 
@@ -622,7 +970,7 @@ int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const d
 {
     return launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, g_plan, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double *key_cams,
@@ -636,7 +984,7 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
 {
     return launch(nullptr, key_img_ptrs, key_cams, T_wk, nullptr, ref_img_ptrs, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, g_plan, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int tdk_update_depth_status(const void *workspace, void *stream)
@@ -664,7 +1012,7 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 int fuse_on_success, int wait_and_check, void *stream)
 {
     if (P <= 0 || R <= 0 || P * R > TDK_STATIC_MAX_PAIRS ||
-        ws_layout(P, R).total > (size_t)TDK_STATIC_SCRATCH_BYTES) {
+        ws_layout(P, R, 1, 1).total_tile > (size_t)TDK_STATIC_SCRATCH_BYTES) {
         tdk_set_error("tdk_update_depth_static_dev: P*R = %lld x %lld exceeds the built-in scratch; this entry "
                       "point takes at most %d keyframe/reference pairs per call (use tdk_update_depth_dev "
                       "with a caller-owned workspace for larger batches)",
@@ -679,7 +1027,7 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
     // pair_setup_kernel.
     rc = launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age, prior_depth,
                 prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag, dbg_argmin, out_hist,
-                fuse_on_success, scratch, (size_t)TDK_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
+                fuse_on_success, PLAN_ONE_KERNEL, scratch, (size_t)TDK_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
     if (rc != TDK_OK || !wait_and_check) return rc;
     return tdk_update_depth_status(scratch, stream);
 }

@@ -103,7 +103,7 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
             _chk(of, "out flag", torch.int64, (P, H, W))
         dbg = torch.empty((P, H, W), dtype=torch.int32, device=dev) if debug else None
         hs = torch.zeros((P, 10), dtype=torch.int64, device=dev) if hist else None
-        nbytes = _lib.update_depth_workspace_bytes(P, R)
+        nbytes = _lib.update_depth_workspace_bytes(P, R, H, W)
         ws = workspace(nbytes, dev, "update_depth")
         rc = _lib.update_depth_dev(_ptr(key_imgs), _ptr(key_cams), _ptr(T_wk), _ptr(ref_imgs),
                                    _ptr(ref_cams), _ptr(T_wr), _ptr(age), _ptr(prior_depth),
@@ -150,7 +150,7 @@ def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, p
         dbg = torch.empty((H, W), dtype=torch.int32, device=dev) if debug else None
         kp = (C.c_void_p * 1)(key_img.data_ptr())
         rp = (C.c_void_p * R)(*[r.data_ptr() for r in ref_imgs])
-        ws = workspace(_lib.update_depth_workspace_bytes(1, R), dev, "update_depth")
+        ws = workspace(_lib.update_depth_workspace_bytes(1, R, H, W), dev, "update_depth")
         rc = _lib.update_depth_frames_dev(kp, _ptr(key_cam), _ptr(T_wk), rp, _ptr(ref_cams),
                                           _ptr(T_wr), _ptr(age), _ptr(prior_depth),
                                           _ptr(prior_variance), pa.ctypes.data_as(C.c_void_p), 1, R,

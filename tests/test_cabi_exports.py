@@ -26,10 +26,10 @@ def test_version_and_error_text_without_a_gpu():
     from tadataka_b200 import _lib
     assert b"sm_100a" in _lib.version()
     # argument validation happens before any CUDA call
-    assert _lib.set_search_lanes(7) == _lib.ERR_INVALID
-    assert b"not in {8,16,32}" in _lib.last_error()
-    assert _lib.update_depth_workspace_bytes(0, 1) == 0
-    assert _lib.update_depth_workspace_bytes(4, 8) > 0
+    assert _lib.set_kernel_plan(7) == _lib.ERR_INVALID
+    assert b"not in {0,1}" in _lib.last_error()
+    assert _lib.update_depth_workspace_bytes(0, 1, 480, 640) == 0
+    assert _lib.update_depth_workspace_bytes(4, 8, 480, 640) >= 4 * 4 * 480 * 640
     assert _lib.propagate_workspace_bytes(1, 480, 640) >= 4 * 4 * 480 * 640
 
 

@@ -70,16 +70,26 @@ def test_c1_single_pair_vga():
     assert_parity(gpu, orc)
 
 
-@pytest.mark.parametrize("lanes", [8, 16, 32])
-def test_search_lanes_do_not_change_results(lanes):
+@pytest.mark.parametrize("plan", [0, 1])
+def test_both_kernel_plans_give_the_oracle_result(plan):
+    """Two kernels with a global candidate queue (default) and one kernel with in-CTA compaction."""
     from tadataka_b200 import _lib
-    b = scene.stack_keyframes([scene.make_pair(1001, H=240, W=320, cam=scene.CAM_VGA / 2)])
-    orc = _oracle(b)
+    sets = [scene.stack_keyframes([scene.make_pair(1001, H=240, W=320, cam=scene.CAM_VGA / 2)]),
+            scene.stack_keyframes([scene.make_keyframe(1002 + i, R=3, H=101, W=147,
+                                                       cam=np.array([120., 118., 73., 50.])) for i in range(3)]),
+            scene.stack_keyframes([scene.make_pair(4100, H=360, W=640, cam=scene.CAM_720P / 2, pset=scene.SET_T)])]
     try:
-        assert _lib.set_search_lanes(lanes) == 0
-        assert_parity(_gpu(b), orc)
+        assert _lib.set_kernel_plan(plan) == 0
+        for b in sets:
+            gpu = _gpu(b, hist=True)
+            orc = _oracle(b)
+            assert_parity(gpu, orc)
+            assert [int(h) for h in gpu[4].sum(0)] == [int((orc[2] == -k).sum()) for k in range(10)]
+            fused = _gpu(b, fuse=True)
+            want_d, want_v = _fuse_reference(b, orc)
+            assert np.array_equal(fused[0], want_d) and np.array_equal(fused[1], want_v)
     finally:
-        _lib.set_search_lanes(16)
+        _lib.set_kernel_plan(0)
 
 
 def test_c2_keyframe_with_8_references_by_age():
