@@ -22,17 +22,18 @@ constexpr int TILE_W = 64;
 constexpr int TILE_H = 4;
 constexpr int BLOCK = TILE_W * TILE_H;
 #ifndef TDK_MIN_CTAS
-#define TDK_MIN_CTAS 3
-#endif
-#ifndef TDK_SAMPLE_CAP
-#define TDK_SAMPLE_CAP 2048
+#define TDK_MIN_CTAS 4
 #endif
 #ifndef TDK_SIEVE_MIN_CTAS
-#define TDK_SIEVE_MIN_CTAS 4
+#define TDK_SIEVE_MIN_CTAS 6
 #endif
 constexpr int MIN_CTAS = TDK_MIN_CTAS;       // resident CTAs per SM the register allocation is tuned for
 constexpr int SIEVE_MIN_CTAS = TDK_SIEVE_MIN_CTAS;
-constexpr int SAMPLE_CAP = TDK_SAMPLE_CAP;   // reference-line samples a CTA stages in shared memory per batch
+constexpr int SORT_BUCKETS = 64;          // phase B sorts a CTA's lines by min(length, 63)
+#ifndef TDK_LONG_LINE
+#define TDK_LONG_LINE 32
+#endif
+constexpr int LONG_LINE = TDK_LONG_LINE;  // lines with more samples than this are searched by a whole warp
 
 struct UpdArgs {
     const TdkKeyConst *keys;
@@ -200,10 +201,13 @@ struct CtaQueue {
     double k[5][BLOCK];                       // key intensities (A1), then the normalised key window (A2)
     double kstep[BLOCK], g[BLOCK], grev[BLOCK], idp[BLOCK], v[BLOCK], xk[BLOCK], yk[BLOCK];
     double xminx[BLOCK], xminy[BLOCK], ux[BLOCK], uy[BLOCK], rdx[BLOCK], rdy[BLOCK];
-    int n[BLOCK], arg[BLOCK], soff[BLOCK + 1], wsum[BLOCK / 32];
+    int n[BLOCK], arg[BLOCK], bucket[SORT_BUCKETS], nlong;
+    unsigned short perm[BLOCK];               // queue slots ordered by line length (phase B)
     int px[BLOCK];                            // x | y << 16 of the pixel
     unsigned short ref[BLOCK], owner[BLOCK];  // reference index; slot of the owning thread (one-kernel plan)
 };
+
+constexpr size_t CTA_DYN_SMEM = sizeof(CtaQueue);
 
 struct A1Result {
     double ki[5];
@@ -366,9 +370,8 @@ __device__ __forceinline__ double window_error(double s0, double s1, double s2, 
 }
 
 // Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
-// argmin is an (error, index) shuffle reduction with the lowest index winning ties.  Used for lines
-// that do not fit the staging buffer.  Returns argmin (0 if no window beat +inf, as
-// intensities.rs:16-29 does) on every lane.
+// argmin is an (error, index) shuffle reduction with the lowest index winning ties.  Returns argmin
+// (0 if no window beat +inf, as intensities.rs:16-29 does) on every lane.
 __device__ __forceinline__ int search_line_warp(const LineGeom &g, int n, double step, int W, int H,
                                                 double k0, double k1, double k2, double k3, double k4, int lane)
 {
@@ -398,93 +401,65 @@ __device__ __forceinline__ int search_line_warp(const LineGeom &g, int n, double
 
 // Phase B for the nq slots of the queue (whole CTA; contains __syncthreads, so every thread must
 // call it with the same nq).  Writes Q.arg[q] = argmin + 2 (intensities.rs:32-36) for live lines.
-// s_buf: SAMPLE_CAP + 4 doubles; s_qid: SAMPLE_CAP line ids.
-__device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, int nq, double *s_buf,
-                                        unsigned short *s_qid)
+//
+// The CTA counting-sorts its lines by length (longest first).  Lines of more than LONG_LINE samples
+// are searched by a whole warp each (search_line_warp).  Every other line is walked by one thread
+// from its first sample to its last, exactly as intensities.rs:16-29 does: a sliding window of five
+// samples in registers, the reference's error for every window, the first minimum kept by
+// `e < best`; thanks to the sort the 32 lines of a warp have (nearly) the same length.
+__device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, int nq)
 {
     const int tid = threadIdx.x, W = a.W, H = a.H;
-    {   // Q.soff = exclusive prefix sum of the line lengths
-        const int v = tid < nq ? Q.n[tid] : 0;
-        const int lane = tid & 31, wid = tid >> 5;
-        int incl = v;
+    if (tid < SORT_BUCKETS) Q.bucket[tid] = 0;
+    __syncthreads();
+    const int n_mine = tid < nq ? Q.n[tid] : 0;
+    const int b_mine = SORT_BUCKETS - 1 - min(n_mine, SORT_BUCKETS - 1);   // long lines first
+    if (tid < nq) atomicAdd(&Q.bucket[b_mine], 1);
+    __syncthreads();
+    if (tid < 32) {   // exclusive prefix sum over the 64 buckets by one warp
+        const int c0 = Q.bucket[2 * tid], c1 = Q.bucket[2 * tid + 1];
+        int incl = c0 + c1;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
             const int o = __shfl_up_sync(0xffffffffu, incl, off);
-            if (lane >= off) incl += o;
+            if (tid >= off) incl += o;
         }
-        if (lane == 31) Q.wsum[wid] = incl;
-        __syncthreads();
-        int woff = 0;
-#pragma unroll
-        for (int w = 0; w < BLOCK / 32; w++) woff += w < wid ? Q.wsum[w] : 0;
-        Q.soff[tid] = woff + incl - v;
-        if (tid == BLOCK - 1) Q.soff[BLOCK] = woff + incl;
+        Q.bucket[2 * tid] = incl - c0 - c1;
+        Q.bucket[2 * tid + 1] = incl - c1;
+        // lines with more than LONG_LINE samples occupy buckets [0, SORT_BUCKETS - 1 - LONG_LINE)
+        constexpr int B0 = SORT_BUCKETS - 1 - LONG_LINE;
+        if (2 * tid == B0) Q.nlong = incl - c0 - c1;
+        if (2 * tid + 1 == B0) Q.nlong = incl - c1;
     }
     __syncthreads();
-    int qa = 0;
-    while (qa < nq) {   // batches of lines whose samples fit the staging buffer (CTA-uniform control flow)
-        const int base = Q.soff[qa];
-        int lo = qa, hi = nq + 1;   // largest qb in (qa, nq] with soff[qb] - base <= SAMPLE_CAP
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (Q.soff[mid] - base <= SAMPLE_CAP) lo = mid; else hi = mid;
-        }
-        const int qb = lo;
-        if (qb == qa) {   // one line longer than the buffer: warp 0 searches it on its own
-            if (tid < 32) {
-                const LineGeom g = line_geom(a, Q, p, qa);
-                const int arg = search_line_warp(g, Q.n[qa], a.step, W, H, Q.k[0][qa], Q.k[1][qa], Q.k[2][qa],
-                                                 Q.k[3][qa], Q.k[4][qa], tid);
-                if (tid == 0) Q.arg[qa] = arg + 2;
-            }
-            qa += 1;
-            continue;
-        }
-        const int S = Q.soff[qb] - base;
-        // pass 0: every line of the batch labels its own stretch of the sample buffer
-        if (tid >= qa && tid < qb) {
-            const int n = Q.n[tid], o = Q.soff[tid] - base;
-            for (int i = 0; i < n; i++) s_qid[o + i] = (unsigned short)tid;
-        }
-        __syncthreads();
-        // pass 1: one sample per thread
-        for (int s = tid; s < S; s += BLOCK) {
-            const int q = s_qid[s];
-            const LineGeom g = line_geom(a, Q, p, q);
-            s_buf[s] = line_sample(g, s - (Q.soff[q] - base), a.step, W, H);
-        }
-        __syncthreads();
-        // pass 2: one window per thread; its error replaces the window's first sample once every
-        // window of the round has been read (later rounds only read later samples)
-        for (int s0 = 0; s0 < S; s0 += BLOCK) {
-            const int s = s0 + tid;
-            double e = INFINITY;
-            if (s < S) {
-                const int q = s_qid[s];
-                const int i = s - (Q.soff[q] - base);
-                if (i < Q.n[q] - 4)
-                    e = window_error(s_buf[s], s_buf[s + 1], s_buf[s + 2], s_buf[s + 3], s_buf[s + 4],
-                                     Q.k[0][q], Q.k[1][q], Q.k[2][q], Q.k[3][q], Q.k[4][q]);
-            }
-            __syncthreads();
-            if (s < S) s_buf[s] = e;
-        }
-        __syncthreads();
-        // pass 3: first minimum of each line, scanned in index order like intensities.rs:16-29
-        if (tid >= qa && tid < qb && Q.n[tid] != 0) {
-            const double *e = s_buf + (Q.soff[tid] - base);
-            const int nwin = Q.n[tid] - 4;
-            double best = INFINITY;
-            int arg = 0;
-            for (int i = 0; i < nwin; i++) {
-                const double ei = e[i];
-                if (ei < best) { best = ei; arg = i; }
-            }
-            Q.arg[tid] = arg + 2;
-        }
-        __syncthreads();
-        qa = qb;
+    if (tid < nq) Q.perm[atomicAdd(&Q.bucket[b_mine], 1)] = (unsigned short)tid;
+    __syncthreads();
+    const int nlong = Q.nlong;
+    for (int r = tid >> 5; r < nlong; r += BLOCK / 32) {   // long lines: one warp each
+        const int q = Q.perm[r];
+        const LineGeom g = line_geom(a, Q, p, q);
+        const int arg = search_line_warp(g, Q.n[q], a.step, W, H, Q.k[0][q], Q.k[1][q], Q.k[2][q], Q.k[3][q],
+                                         Q.k[4][q], tid & 31);
+        if ((tid & 31) == 0) Q.arg[q] = arg + 2;
     }
+    const int r = nlong + tid;   // the other lines: one thread each
+    if (r >= nq) return;
+    const int q = Q.perm[r];
+    const int n = Q.n[q];
+    if (n == 0) return;   // dropped in A2
+    const LineGeom g = line_geom(a, Q, p, q);
+    const double k0 = Q.k[0][q], k1 = Q.k[1][q], k2 = Q.k[2][q], k3 = Q.k[3][q], k4 = Q.k[4][q];
+    double s0 = line_sample(g, 0, a.step, W, H), s1 = line_sample(g, 1, a.step, W, H);
+    double s2 = line_sample(g, 2, a.step, W, H), s3 = line_sample(g, 3, a.step, W, H);
+    double best = INFINITY;
+    int arg = 0;
+    for (int i = 0; i + 4 < n; i++) {
+        const double s4 = line_sample(g, i + 4, a.step, W, H);
+        const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+        if (e < best) { best = e; arg = i; }
+        s0 = s1; s1 = s2; s2 = s3; s3 = s4;
+    }
+    Q.arg[q] = arg + 2;
 }
 
 // Phase C for a live queue slot q.  Returns the final flag; on SUCCESS nd / nv hold the new (or
@@ -570,16 +545,14 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
 // ~5-15 % of candidates populate phases A2/B/C.
 __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(const UpdArgs a)
 {
-    __shared__ CtaQueue Q;
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    CtaQueue &Q = *reinterpret_cast<CtaQueue *>(s_dyn);
     __shared__ double s_depth[BLOCK], s_var[BLOCK];
     __shared__ int s_arg[BLOCK];
     __shared__ signed char s_flag[BLOCK];
     __shared__ double s_xk[TILE_W], s_yk[TILE_H];    // normalised key coordinates of the tile
     __shared__ int s_nq;
     __shared__ unsigned int s_hist[10];
-    extern __shared__ double s_dyn[];                // SAMPLE_CAP + 4 samples, then SAMPLE_CAP line ids
-    double *const s_buf = s_dyn;
-    unsigned short *const s_qid = (unsigned short *)(s_dyn + SAMPLE_CAP + 4);
 
     const int tid = threadIdx.x;
     const int tiles = a.tiles_x * a.tiles_y;
@@ -633,7 +606,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
     }
     __syncthreads();
 
-    phase_b(a, Q, p, nq, s_buf, s_qid);
+    phase_b(a, Q, p, nq);
+    __syncthreads();
 
     // ---- phase C
     if (tid < nq && Q.n[tid] != 0) {
@@ -670,7 +644,6 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
 {
     __shared__ double s_xk[TILE_W], s_yk[TILE_H];
     __shared__ unsigned int s_hist[10];
-    __shared__ int s_cnt, s_base;
 
     const int tid = threadIdx.x;
     const int tiles = a.tiles_x * a.tiles_y;
@@ -682,7 +655,6 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     const TdkKeyConst key = a.keys[p];
     const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
 
-    if (tid == 0) s_cnt = 0;
     if (tid < 10) s_hist[tid] = 0;
     if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
     else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
@@ -692,7 +664,7 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
     const bool valid = x < W && y < H;
     const size_t pix = map_base + (size_t)y * W + x;
-    int flag = TDK_FLAG_NOT_PROCESSED, slot = -1;
+    int flag = TDK_FLAG_NOT_PROCESSED;
     if (valid) {
         const uint64_t age = a.age[pix];
         const double d = a.prior_d[pix], v = a.prior_v[pix];
@@ -703,7 +675,6 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
             } else {
                 A1Result c;
                 flag = phase_a1(a, key, p, s_xk[lx], s_yk[ly], age, d, v, wm1, hm1, out_d, c);
-                if (flag == 1) slot = atomicAdd(&s_cnt, 1);
             }
         }
         // candidates get the values a failed estimate keeps; search_kernel overwrites them on success
@@ -713,20 +684,26 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
         if (a.dbg) a.dbg[pix] = -1;
         if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
     }
-    __syncthreads();
-    if (tid == 0 && s_cnt > 0) s_base = (int)atomicAdd(a.cand_count + p, (unsigned int)s_cnt);
-    __syncthreads();
-    if (slot >= 0) a.cand[map_base + (size_t)(s_base + slot)] = (unsigned int)(y * W + x);
-    if (a.hist && tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+    // append this warp's candidates to the keyframe's queue: one global atomic per warp, no CTA barrier
+    const unsigned cmask = __ballot_sync(0xffffffffu, flag == 1);
+    if (cmask) {
+        const int lane = tid & 31;
+        unsigned int base = 0;
+        if (lane == 0) base = atomicAdd(a.cand_count + p, (unsigned int)__popc(cmask));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (flag == 1) a.cand[map_base + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
+    }
+    if (a.hist) {
+        __syncthreads();
+        if (tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+    }
 }
 
 __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(const UpdArgs a)
 {
-    __shared__ CtaQueue Q;
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    CtaQueue &Q = *reinterpret_cast<CtaQueue *>(s_dyn);
     __shared__ unsigned int s_hist[10];
-    extern __shared__ double s_dyn[];
-    double *const s_buf = s_dyn;
-    unsigned short *const s_qid = (unsigned short *)(s_dyn + SAMPLE_CAP + 4);
 
     const int tid = threadIdx.x;
     const int chunks = a.tiles_x * a.tiles_y;   // ceil(H*W / BLOCK)
@@ -760,7 +737,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     }
     __syncthreads();
 
-    phase_b(a, Q, p, nq, s_buf, s_qid);
+    phase_b(a, Q, p, nq);
+    __syncthreads();
 
     // ---- phase C and the scattered store of this CTA's candidates
     if (tid < nq) {
@@ -807,7 +785,7 @@ WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W)
 
 enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1 };
 int g_plan = PLAN_TWO_KERNELS;
-constexpr size_t FLAT_DYN_SMEM = (SAMPLE_CAP + 4) * sizeof(double) + SAMPLE_CAP * sizeof(unsigned short);
+constexpr size_t FLAT_DYN_SMEM = CTA_DYN_SMEM;
 
 int launch(const double *key_imgs, const double *const *key_ptrs_host, const double *key_cams,
            const double *T_wk, const double *ref_imgs, const double *const *ref_ptrs_host,
