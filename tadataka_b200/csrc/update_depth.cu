@@ -369,99 +369,6 @@ __device__ __forceinline__ double window_error(double s0, double s1, double s2, 
     return d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
 }
 
-// Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
-// argmin is an (error, index) shuffle reduction with the lowest index winning ties.  Returns argmin
-// (0 if no window beat +inf, as intensities.rs:16-29 does) on every lane.
-__device__ __forceinline__ int search_line_warp(const LineGeom &g, int n, double step, int W, int H,
-                                                double k0, double k1, double k2, double k3, double k4, int lane)
-{
-    const int nwin = n - 4;
-    double best_e = INFINITY;
-    int best_i = 0x7fffffff;
-    for (int base = 0; base < nwin; base += 28) {
-        const int i = base + lane;
-        const double s0 = i < n ? line_sample(g, i, step, W, H) : 0.;
-        const double s1 = __shfl_down_sync(0xffffffffu, s0, 1);
-        const double s2 = __shfl_down_sync(0xffffffffu, s0, 2);
-        const double s3 = __shfl_down_sync(0xffffffffu, s0, 3);
-        const double s4 = __shfl_down_sync(0xffffffffu, s0, 4);
-        if (lane < 28 && i < nwin) {
-            const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
-            if (e < best_e) { best_e = e; best_i = i; }
-        }
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        const double oe = __shfl_xor_sync(0xffffffffu, best_e, off);
-        const int oi = __shfl_xor_sync(0xffffffffu, best_i, off);
-        if (oe < best_e || (oe == best_e && oi < best_i)) { best_e = oe; best_i = oi; }
-    }
-    return best_i == 0x7fffffff ? 0 : best_i;
-}
-
-// Phase B for the nq slots of the queue (whole CTA; contains __syncthreads, so every thread must
-// call it with the same nq).  Writes Q.arg[q] = argmin + 2 (intensities.rs:32-36) for live lines.
-//
-// The CTA counting-sorts its lines by length (longest first).  Lines of more than LONG_LINE samples
-// are searched by a whole warp each (search_line_warp).  Every other line is walked by one thread
-// from its first sample to its last, exactly as intensities.rs:16-29 does: a sliding window of five
-// samples in registers, the reference's error for every window, the first minimum kept by
-// `e < best`; thanks to the sort the 32 lines of a warp have (nearly) the same length.
-__device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, int nq)
-{
-    const int tid = threadIdx.x, W = a.W, H = a.H;
-    if (tid < SORT_BUCKETS) Q.bucket[tid] = 0;
-    __syncthreads();
-    const int n_mine = tid < nq ? Q.n[tid] : 0;
-    const int b_mine = SORT_BUCKETS - 1 - min(n_mine, SORT_BUCKETS - 1);   // long lines first
-    if (tid < nq) atomicAdd(&Q.bucket[b_mine], 1);
-    __syncthreads();
-    if (tid < 32) {   // exclusive prefix sum over the 64 buckets by one warp
-        const int c0 = Q.bucket[2 * tid], c1 = Q.bucket[2 * tid + 1];
-        int incl = c0 + c1;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, incl, off);
-            if (tid >= off) incl += o;
-        }
-        Q.bucket[2 * tid] = incl - c0 - c1;
-        Q.bucket[2 * tid + 1] = incl - c1;
-        // lines with more than LONG_LINE samples occupy buckets [0, SORT_BUCKETS - 1 - LONG_LINE)
-        constexpr int B0 = SORT_BUCKETS - 1 - LONG_LINE;
-        if (2 * tid == B0) Q.nlong = incl - c0 - c1;
-        if (2 * tid + 1 == B0) Q.nlong = incl - c1;
-    }
-    __syncthreads();
-    if (tid < nq) Q.perm[atomicAdd(&Q.bucket[b_mine], 1)] = (unsigned short)tid;
-    __syncthreads();
-    const int nlong = Q.nlong;
-    for (int r = tid >> 5; r < nlong; r += BLOCK / 32) {   // long lines: one warp each
-        const int q = Q.perm[r];
-        const LineGeom g = line_geom(a, Q, p, q);
-        const int arg = search_line_warp(g, Q.n[q], a.step, W, H, Q.k[0][q], Q.k[1][q], Q.k[2][q], Q.k[3][q],
-                                         Q.k[4][q], tid & 31);
-        if ((tid & 31) == 0) Q.arg[q] = arg + 2;
-    }
-    const int r = nlong + tid;   // the other lines: one thread each
-    if (r >= nq) return;
-    const int q = Q.perm[r];
-    const int n = Q.n[q];
-    if (n == 0) return;   // dropped in A2
-    const LineGeom g = line_geom(a, Q, p, q);
-    const double k0 = Q.k[0][q], k1 = Q.k[1][q], k2 = Q.k[2][q], k3 = Q.k[3][q], k4 = Q.k[4][q];
-    double s0 = line_sample(g, 0, a.step, W, H), s1 = line_sample(g, 1, a.step, W, H);
-    double s2 = line_sample(g, 2, a.step, W, H), s3 = line_sample(g, 3, a.step, W, H);
-    double best = INFINITY;
-    int arg = 0;
-    for (int i = 0; i + 4 < n; i++) {
-        const double s4 = line_sample(g, i + 4, a.step, W, H);
-        const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
-        if (e < best) { best = e; arg = i; }
-        s0 = s1; s1 = s2; s2 = s3; s3 = s4;
-    }
-    Q.arg[q] = arg + 2;
-}
-
 // Phase C for a live queue slot q.  Returns the final flag; on SUCCESS nd / nv hold the new (or
 // fused) depth and variance.
 __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, const TdkKeyConst &key, int p, int q,
@@ -539,6 +446,108 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
     return f;
 }
 
+// Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
+// argmin is an (error, index) shuffle reduction with the lowest index winning ties.  Returns argmin
+// (0 if no window beat +inf, as intensities.rs:16-29 does) on every lane.
+__device__ __forceinline__ int search_line_warp(const LineGeom &g, int n, double step, int W, int H,
+                                                double k0, double k1, double k2, double k3, double k4, int lane)
+{
+    const int nwin = n - 4;
+    double best_e = INFINITY;
+    int best_i = 0x7fffffff;
+    for (int base = 0; base < nwin; base += 28) {
+        const int i = base + lane;
+        const double s0 = i < n ? line_sample(g, i, step, W, H) : 0.;
+        const double s1 = __shfl_down_sync(0xffffffffu, s0, 1);
+        const double s2 = __shfl_down_sync(0xffffffffu, s0, 2);
+        const double s3 = __shfl_down_sync(0xffffffffu, s0, 3);
+        const double s4 = __shfl_down_sync(0xffffffffu, s0, 4);
+        if (lane < 28 && i < nwin) {
+            const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+            if (e < best_e) { best_e = e; best_i = i; }
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const double oe = __shfl_xor_sync(0xffffffffu, best_e, off);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, off);
+        if (oe < best_e || (oe == best_e && oi < best_i)) { best_e = oe; best_i = oi; }
+    }
+    return best_i == 0x7fffffff ? 0 : best_i;
+}
+
+// Phase B for the nq slots of the queue (whole CTA; contains __syncthreads, so every thread must
+// call it with the same nq).  Writes Q.arg[q] = argmin + 2 (intensities.rs:32-36) for each live line
+// and then calls finish(q) -- phase C and whatever the kernel does with its result -- from the
+// thread that searched the line, so no CTA barrier separates the search from phase C and a warp
+// that is done with its lines never waits for the warp holding the longest ones.
+//
+// The CTA counting-sorts its lines by length (longest first).  Lines of more than LONG_LINE samples
+// are searched by a whole warp each (search_line_warp).  Every other line is walked by one thread
+// from its first sample to its last, exactly as intensities.rs:16-29 does: a sliding window of five
+// samples in registers, the reference's error for every window, the first minimum kept by
+// `e < best`; thanks to the sort the 32 lines of a warp have (nearly) the same length.
+template <typename Finish>
+__device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, int nq, Finish finish)
+{
+    const int tid = threadIdx.x, W = a.W, H = a.H;
+    if (tid < SORT_BUCKETS) Q.bucket[tid] = 0;
+    __syncthreads();
+    const int n_mine = tid < nq ? Q.n[tid] : 0;
+    const int b_mine = SORT_BUCKETS - 1 - min(n_mine, SORT_BUCKETS - 1);   // long lines first
+    if (tid < nq) atomicAdd(&Q.bucket[b_mine], 1);
+    __syncthreads();
+    if (tid < 32) {   // exclusive prefix sum over the 64 buckets by one warp
+        const int c0 = Q.bucket[2 * tid], c1 = Q.bucket[2 * tid + 1];
+        int incl = c0 + c1;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (tid >= off) incl += o;
+        }
+        Q.bucket[2 * tid] = incl - c0 - c1;
+        Q.bucket[2 * tid + 1] = incl - c1;
+        // lines with more than LONG_LINE samples occupy buckets [0, SORT_BUCKETS - 1 - LONG_LINE)
+        constexpr int B0 = SORT_BUCKETS - 1 - LONG_LINE;
+        if (2 * tid == B0) Q.nlong = incl - c0 - c1;
+        if (2 * tid + 1 == B0) Q.nlong = incl - c1;
+    }
+    __syncthreads();
+    if (tid < nq) Q.perm[atomicAdd(&Q.bucket[b_mine], 1)] = (unsigned short)tid;
+    __syncthreads();
+    const int nlong = Q.nlong;
+    for (int r = tid >> 5; r < nlong; r += BLOCK / 32) {   // long lines: one warp each
+        const int q = Q.perm[r];
+        const LineGeom g = line_geom(a, Q, p, q);
+        const int arg = search_line_warp(g, Q.n[q], a.step, W, H, Q.k[0][q], Q.k[1][q], Q.k[2][q], Q.k[3][q],
+                                         Q.k[4][q], tid & 31);
+        if ((tid & 31) == 0) Q.arg[q] = arg + 2;
+    }
+    if (nlong > 0) {   // phase C of the long lines this warp searched, one lane per line
+        __syncwarp();
+        for (int r = (tid >> 5) + (BLOCK / 32) * (tid & 31); r < nlong; r += BLOCK) finish((int)Q.perm[r]);
+    }
+    const int r = nlong + tid;   // the other lines: one thread each
+    if (r >= nq) return;
+    const int q = Q.perm[r];
+    const int n = Q.n[q];
+    if (n == 0) return;   // dropped in A2
+    const LineGeom g = line_geom(a, Q, p, q);
+    const double k0 = Q.k[0][q], k1 = Q.k[1][q], k2 = Q.k[2][q], k3 = Q.k[3][q], k4 = Q.k[4][q];
+    double s0 = line_sample(g, 0, a.step, W, H), s1 = line_sample(g, 1, a.step, W, H);
+    double s2 = line_sample(g, 2, a.step, W, H), s3 = line_sample(g, 3, a.step, W, H);
+    double best = INFINITY;
+    int arg = 0;
+    for (int i = 0; i + 4 < n; i++) {
+        const double s4 = line_sample(g, i + 4, a.step, W, H);
+        const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+        if (e < best) { best = e; arg = i; }
+        s0 = s1; s1 = s2; s2 = s3; s3 = s4;
+    }
+    Q.arg[q] = arg + 2;
+    finish(q);
+}
+
 // ---------------------------------------------------------------------------------------------
 // One-kernel plan: a CTA owns a 64x4 tile, compacts its own candidates and runs every phase.
 // Needs no global queue (this is what tdk_update_depth_static_dev runs), but only the tile's own
@@ -555,10 +564,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int tiles = a.tiles_x * a.tiles_y;
-    const int p = blockIdx.x / tiles;
-    const int t = blockIdx.x - p * tiles;
-    const int ty = t / a.tiles_x, tx = t - ty * a.tiles_x;
+    const int p = blockIdx.z;
+    const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t map_base = (size_t)p * H * W;
     const TdkKeyConst key = a.keys[p];
@@ -606,18 +613,15 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
     }
     __syncthreads();
 
-    phase_b(a, Q, p, nq);
-    __syncthreads();
-
-    // ---- phase C
-    if (tid < nq && Q.n[tid] != 0) {
+    // ---- phases B and C
+    phase_b(a, Q, p, nq, [&](int q) {
         double nd, nv;
-        const int f = phase_c(a, Q, key, p, tid, map_base, nd, nv);
-        const int owner = Q.owner[tid];
+        const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
+        const int owner = Q.owner[q];
         if (f == TDK_FLAG_SUCCESS) { s_depth[owner] = nd; s_var[owner] = nv; }
         s_flag[owner] = (signed char)f;
-        s_arg[owner] = Q.arg[tid];
-    }
+        s_arg[owner] = Q.arg[q];
+    });
     __syncthreads();
 
     // ---- store
@@ -646,28 +650,29 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int tiles = a.tiles_x * a.tiles_y;
-    const int p = blockIdx.x / tiles;
-    const int t = blockIdx.x - p * tiles;
-    const int ty = t / a.tiles_x, tx = t - ty * a.tiles_x;
+    const int p = blockIdx.z;
+    const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
     const TdkKeyConst key = a.keys[p];
     const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
+
+    const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
+    const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
+    const bool valid = x < W && y < H;
+    const size_t pix = map_base + (size_t)y * W + x;
+    // the three map loads go out first, so their DRAM latency overlaps the table set-up below
+    uint64_t age = 0;
+    double d = 0., v = 0.;
+    if (valid) { age = a.age[pix]; d = a.prior_d[pix]; v = a.prior_v[pix]; }
 
     if (tid < 10) s_hist[tid] = 0;
     if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
     else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
     __syncthreads();
 
-    const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
-    const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
-    const bool valid = x < W && y < H;
-    const size_t pix = map_base + (size_t)y * W + x;
     int flag = TDK_FLAG_NOT_PROCESSED;
     if (valid) {
-        const uint64_t age = a.age[pix];
-        const double d = a.prior_d[pix], v = a.prior_v[pix];
         double out_d = d;
         if (age != 0) {
             if (age > (uint64_t)a.R) {
@@ -706,9 +711,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int chunks = a.tiles_x * a.tiles_y;   // ceil(H*W / BLOCK)
-    const int p = blockIdx.x / chunks;
-    const int chunk = blockIdx.x - p * chunks;
+    const int p = blockIdx.z;
+    const int chunk = blockIdx.y * gridDim.x + blockIdx.x;   // over ceil(H*W / BLOCK) chunks of the queue
     const int total = (int)a.cand_count[p];
     const int first = chunk * BLOCK;
     if (first >= total) return;
@@ -718,6 +722,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     const TdkKeyConst key = a.keys[p];
     const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
     if (tid < 10) s_hist[tid] = 0;
+    __syncthreads();
 
     // ---- phase A1 again for this CTA's candidates (same arithmetic, so they all pass again), then A2
     int flag = 1;
@@ -734,25 +739,23 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
         phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
         queue_push(Q, tid, c, v, xk, yk, x, y, tid);
         flag = phase_a2(a, Q, p, tid, wm1, hm1);
-    }
-    __syncthreads();
-
-    phase_b(a, Q, p, nq);
-    __syncthreads();
-
-    // ---- phase C and the scattered store of this CTA's candidates
-    if (tid < nq) {
-        int arg = -1;
-        if (flag == 1) {
-            double nd, nv;
-            flag = phase_c(a, Q, key, p, tid, map_base, nd, nv);
-            arg = Q.arg[tid];
-            if (flag == TDK_FLAG_SUCCESS) { a.out_d[pix] = nd; a.out_v[pix] = nv; }
+        if (flag != 1) {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
+            a.out_f[pix] = (long long)flag;
+            if (a.hist) atomicAdd(&s_hist[-flag], 1u);
         }
-        if (flag != TDK_FLAG_SUCCESS) a.out_f[pix] = (long long)flag;
-        if (a.dbg) a.dbg[pix] = arg;
-        if (a.hist) atomicAdd(&s_hist[-flag], 1u);
     }
+    __syncthreads();
+
+    // ---- phases B and C, then the scattered store, all by the thread that searched the line
+    phase_b(a, Q, p, nq, [&](int q) {
+        double nd, nv;
+        const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
+        const size_t at = map_base + (size_t)(Q.px[q] >> 16) * W + (Q.px[q] & 0xffff);
+        if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
+        else a.out_f[at] = (long long)f;
+        if (a.dbg) a.dbg[at] = Q.arg[q];
+        if (a.hist) atomicAdd(&s_hist[-f], 1u);
+    });
     if (a.hist) {
         __syncthreads();
         if (tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
@@ -818,10 +821,12 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     }
     const int tiles_x = (int)((W + TILE_W - 1) / TILE_W), tiles_y = (int)((H + TILE_H - 1) / TILE_H);
     const long long nblocks = (long long)P * tiles_x * tiles_y;
-    if (nblocks > 2147483647LL || P * R > 2147483647LL) {
-        tdk_set_error("tdk_update_depth: batch too large for one launch (%lld tiles)", nblocks);
+    if (nblocks > 2147483647LL || P * R > 2147483647LL || P > 65535 || tiles_y > 65535) {
+        tdk_set_error("tdk_update_depth: batch too large for one launch (P=%lld, %lld tiles; at most 65535 "
+                      "keyframes per call)", (long long)P, nblocks);
         return TDK_ERR_INVALID;
     }
+    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)P);
     char *ws = (char *)workspace;
     int *status = (int *)(ws + l.status);
     TdkKeyConst *keys = (TdkKeyConst *)(ws + l.keys);
@@ -865,14 +870,14 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     }
     if (plan == PLAN_ONE_KERNEL) {
         a.cand = nullptr; a.cand_count = nullptr;
-        update_depth_tile_kernel<<<(unsigned)nblocks, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+        update_depth_tile_kernel<<<grid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
     } else {
         a.cand_count = (unsigned int *)(ws + l.cand_count);
         a.cand = (unsigned int *)(ws + l.cand);
         TDK_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)P * sizeof(unsigned int), stream));
-        update_depth_sieve_kernel<<<(unsigned)nblocks, BLOCK, 0, stream>>>(a);
+        update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
         TDK_CUDA(cudaGetLastError());
-        update_depth_search_kernel<<<(unsigned)nblocks, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+        update_depth_search_kernel<<<grid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
