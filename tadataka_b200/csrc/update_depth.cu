@@ -712,11 +712,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
 
     const int tid = threadIdx.x;
     const int p = blockIdx.z;
-    const int chunk = blockIdx.y * gridDim.x + blockIdx.x;   // over ceil(H*W / BLOCK) chunks of the queue
     const int total = (int)a.cand_count[p];
-    const int first = chunk * BLOCK;
-    if (first >= total) return;
-    const int nq = min(BLOCK, total - first);
     const int W = a.W, H = a.H;
     const size_t map_base = (size_t)p * H * W;
     const TdkKeyConst key = a.keys[p];
@@ -724,38 +720,42 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     if (tid < 10) s_hist[tid] = 0;
     __syncthreads();
 
-    // ---- phase A1 again for this CTA's candidates (same arithmetic, so they all pass again), then A2
-    int flag = 1;
-    size_t pix = 0;
-    double fail_d = 0.;
-    if (tid < nq) {
-        const unsigned int li = a.cand[map_base + first + tid];
-        const int y = (int)(li / (unsigned int)W), x = (int)(li - (unsigned int)y * W);
-        pix = map_base + li;
-        const uint64_t age = a.age[pix];
-        const double d = a.prior_d[pix], v = a.prior_v[pix];
-        const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
-        A1Result c;
-        phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
-        queue_push(Q, tid, c, v, xk, yk, x, y, tid);
-        flag = phase_a2(a, Q, p, tid, wm1, hm1);
-        if (flag != 1) {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
-            a.out_f[pix] = (long long)flag;
-            if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+    // the grid holds a quarter of the keyframe's tiles per keyframe (usually 5-15 % of the pixels
+    // are queued); CTAs stride over the queue in chunks of BLOCK candidates
+    for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
+        const int nq = min(BLOCK, total - first);
+        // ---- phase A1 again for this chunk's candidates (same arithmetic, so they all pass again), then A2
+        if (tid < nq) {
+            const unsigned int li = a.cand[map_base + first + tid];
+            const int y = (int)(li / (unsigned int)W), x = (int)(li - (unsigned int)y * W);
+            const size_t pix = map_base + li;
+            const uint64_t age = a.age[pix];
+            const double d = a.prior_d[pix], v = a.prior_v[pix];
+            const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
+            A1Result c;
+            double fail_d;
+            phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
+            queue_push(Q, tid, c, v, xk, yk, x, y, tid);
+            const int flag = phase_a2(a, Q, p, tid, wm1, hm1);
+            if (flag != 1) {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
+                a.out_f[pix] = (long long)flag;
+                if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+            }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- phases B and C, then the scattered store, all by the thread that searched the line
-    phase_b(a, Q, p, nq, [&](int q) {
-        double nd, nv;
-        const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
-        const size_t at = map_base + (size_t)(Q.px[q] >> 16) * W + (Q.px[q] & 0xffff);
-        if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
-        else a.out_f[at] = (long long)f;
-        if (a.dbg) a.dbg[at] = Q.arg[q];
-        if (a.hist) atomicAdd(&s_hist[-f], 1u);
-    });
+        // ---- phases B and C, then the scattered store, all by the thread that searched the line
+        phase_b(a, Q, p, nq, [&](int q) {
+            double nd, nv;
+            const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
+            const size_t at = map_base + (size_t)(Q.px[q] >> 16) * W + (Q.px[q] & 0xffff);
+            if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
+            else a.out_f[at] = (long long)f;
+            if (a.dbg) a.dbg[at] = Q.arg[q];
+            if (a.hist) atomicAdd(&s_hist[-f], 1u);
+        });
+        __syncthreads();   // the queue is reused by the next chunk
+    }
     if (a.hist) {
         __syncthreads();
         if (tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
@@ -877,7 +877,8 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         TDK_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)P * sizeof(unsigned int), stream));
         update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
         TDK_CUDA(cudaGetLastError());
-        update_depth_search_kernel<<<grid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+        const dim3 sgrid((unsigned)((tiles_x * tiles_y + 3) / 4), 1u, (unsigned)P);
+        update_depth_search_kernel<<<sgrid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;

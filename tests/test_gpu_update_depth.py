@@ -127,6 +127,19 @@ def test_ragged_image_size_and_edge_tiles():
     assert_parity(_gpu(b), _oracle(b))
 
 
+def test_dense_texture_most_pixels_reach_the_search():
+    """White-noise images: nearly every pixel passes the gradient test, so the candidate queue holds
+    far more than a quarter of the pixels and the search kernel's CTAs loop over several chunks."""
+    rng = np.random.default_rng(42)
+    it = scene.make_keyframe(43, R=2, H=120, W=192, cam=np.array([150., 150., 95.5, 59.5]))
+    it["key_img"] = rng.random((120, 192))
+    it["ref_imgs"] = rng.random((2, 120, 192))
+    b = scene.stack_keyframes([it, it])
+    gpu, orc = _gpu(b), _oracle(b)
+    assert (orc[3] >= 0).mean() > 0.5          # more than half of all pixels were searched
+    assert_parity(gpu, orc)
+
+
 def test_every_flag_is_reachable_and_matches():
     """Hand-made priors that drive pixels into each failure branch (hypothesis.rs:21-37,
     semi_dense.rs:27-40,62-81): negative prior, out-of-range hypothesis, behind the reference."""
