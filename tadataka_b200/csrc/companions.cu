@@ -42,29 +42,44 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
 // -------------------------------------------------------------------------------- regularize
 // regularization.rs:29-64 : sum over the zero-padded 3x3 (row-major) of id*iv / sum of iv where
 // flag == Success; no Success cell -> the input depth is kept.
+// A CTA stages id*iv and iv of its 64x4 tile plus a one-pixel halo in shared memory (two
+// inversions per pixel instead of two per neighbour visit); cells the reference skips hold exact
+// zeros, which leave its left-to-right sums unchanged.
+constexpr int RT_W = 64, RT_H = 4;
 __global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restrict__ depth,
                                                          const double *__restrict__ variance,
                                                          const long long *__restrict__ flag, int P, int H,
                                                          int W, double *__restrict__ out)
 {
-    const int x = blockIdx.x * 64 + (threadIdx.x & 63);
-    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
-    const int p = blockIdx.z;
+    __shared__ double s_prod[RT_H + 2][RT_W + 2], s_iv[RT_H + 2][RT_W + 2];
+    const int x0 = blockIdx.x * RT_W, y0 = blockIdx.y * RT_H;
+    const size_t base = (size_t)blockIdx.z * H * W;
+    for (int e = threadIdx.x; e < (RT_H + 2) * (RT_W + 2); e += TPB) {
+        const int hy = e / (RT_W + 2), hx = e - hy * (RT_W + 2);
+        const int yy = y0 - 1 + hy, xx = x0 - 1 + hx;
+        double prod = 0., iv = 0.;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+            const size_t i = base + (size_t)yy * W + xx;
+            if (__ldg(flag + i) == TDK_FLAG_SUCCESS) {
+                const double id = tdk::inv(__ldg(depth + i));
+                iv = tdk::inv(__ldg(variance + i));
+                prod = id * iv;
+            }
+        }
+        s_prod[hy][hx] = prod;
+        s_iv[hy][hx] = iv;
+    }
+    __syncthreads();
+    const int lx = threadIdx.x & (RT_W - 1), ly = threadIdx.x / RT_W;
+    const int x = x0 + lx, y = y0 + ly;
     if (x >= W || y >= H) return;
-    const size_t base = (size_t)p * H * W;
     double num = 0., den = 0.;
 #pragma unroll
-    for (int dy = -1; dy <= 1; dy++) {
+    for (int dy = 0; dy < 3; dy++) {
 #pragma unroll
-        for (int dx = -1; dx <= 1; dx++) {
-            const int yy = y + dy, xx = x + dx;
-            if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
-            const size_t i = base + (size_t)yy * W + xx;
-            if (__ldg(flag + i) != TDK_FLAG_SUCCESS) continue;
-            const double id = tdk::inv(__ldg(depth + i));
-            const double iv = tdk::inv(__ldg(variance + i));
-            num = num + id * iv;
-            den = den + iv;
+        for (int dx = 0; dx < 3; dx++) {
+            num = num + s_prod[ly + dy][lx + dx];
+            den = den + s_iv[ly + dy][lx + dx];
         }
     }
     const size_t c = base + (size_t)y * W + x;
@@ -94,6 +109,17 @@ __device__ __forceinline__ FrameConst load_frame_const(const double *__restrict_
     return c;
 }
 
+__device__ __forceinline__ int warp_target_n(const FrameConst &c, double qx, double qy, double depth0, int H,
+                                             int W, double &depth1)
+{
+    double x1, y1;
+    tdk::warp_point(c.T, qx, qy, depth0, x1, y1, depth1);
+    const double u = x1 * c.f1x + c.o1x;
+    const double v = y1 * c.f1y + c.o1y;
+    if (!tdk::in_range(u, v, (double)W - 1., (double)H - 1.)) return -1;
+    return (int)v * W + (int)u;
+}
+
 __device__ __forceinline__ int warp_target(const FrameConst &c, int x0, int y0, double depth0, int H,
                                            int W, double &depth1)
 {
@@ -110,19 +136,38 @@ __device__ __forceinline__ int warp_target(const FrameConst &c, int x0, int y0, 
 // ----------------------------------------------------------------------------- increment_age
 // age.rs:6-32.  The raster-order "last writer wins" becomes: the winner of a target is the source
 // with the largest linear index (atomicMax), then one gather pass writes age0[winner] + 1.
+// Source pixels are visited in 64x4 tiles; K0^-1 u0 depends on the column (row) only, so a tile
+// computes 64 + 4 divisions instead of two per pixel (camera.rs:55-57).
+__device__ __forceinline__ bool tile_source(const FrameConst &c, int H, int W, double *s_qx, double *s_qy,
+                                            int &x, int &y, double &qx, double &qy)
+{
+    const int tid = threadIdx.x;
+    if (tid < RT_W) s_qx[tid] = ((double)(blockIdx.x * RT_W + tid) - c.o0x) / c.f0x;
+    else if (tid < RT_W + RT_H) s_qy[tid - RT_W] = ((double)(blockIdx.y * RT_H + tid - RT_W) - c.o0y) / c.f0y;
+    __syncthreads();
+    const int lx = tid & (RT_W - 1), ly = tid / RT_W;
+    x = blockIdx.x * RT_W + lx;
+    y = blockIdx.y * RT_H + ly;
+    qx = s_qx[lx];
+    qy = s_qy[ly];
+    return x < W && y < H;
+}
+
 __global__ void __launch_bounds__(TPB) age_scatter_kernel(const double *__restrict__ T10,
                                                           const double *__restrict__ cam0,
                                                           const double *__restrict__ cam1,
                                                           const double *__restrict__ depth0, int H, int W,
                                                           unsigned int *__restrict__ winner)
 {
-    const int p = blockIdx.y;
+    __shared__ double s_qx[RT_W], s_qy[RT_H];
+    const int p = blockIdx.z;
     const int hw = H * W;
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= hw) return;
     const FrameConst c = load_frame_const(T10, cam0, cam1, p);
-    double d1;
-    const int t = warp_target(c, s % W, s / W, depth0[(size_t)p * hw + s], H, W, d1);
+    int x, y;
+    double qx, qy, d1;
+    if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
+    const int s = y * W + x;
+    const int t = warp_target_n(c, qx, qy, depth0[(size_t)p * hw + s], H, W, d1);
     if (t >= 0) atomicMax(winner + (size_t)p * hw + t, (unsigned int)s + 1u);
 }
 
@@ -148,13 +193,15 @@ __global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restric
                                                          const double *__restrict__ depth0, int H, int W,
                                                          int *__restrict__ tgt, unsigned int *__restrict__ cnt)
 {
-    const int p = blockIdx.y;
+    __shared__ double s_qx[RT_W], s_qy[RT_H];
+    const int p = blockIdx.z;
     const int hw = H * W;
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= hw) return;
     const FrameConst c = load_frame_const(T10, cam0, cam1, p);
-    double d1;
-    const int t = warp_target(c, s % W, s / W, depth0[(size_t)p * hw + s], H, W, d1);
+    int x, y;
+    double qx, qy, d1;
+    if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
+    const int s = y * W + x;
+    const int t = warp_target_n(c, qx, qy, depth0[(size_t)p * hw + s], H, W, d1);
     tgt[(size_t)p * hw + s] = t;
     if (t >= 0) atomicAdd(cnt + (size_t)p * hw + t, 1u);
 }
@@ -438,7 +485,8 @@ int tdk_increment_age_dev(const uint64_t *age0, const double *cam0, const double
     unsigned int *winner = (unsigned int *)workspace;
     TDK_CUDA(cudaMemsetAsync(winner, 0, (size_t)P * hw * 4, st));
     dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
-    age_scatter_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, winner);
+    dim3 tgrid((unsigned)((W + RT_W - 1) / RT_W), (unsigned)((H + RT_H - 1) / RT_H), (unsigned)P);
+    age_scatter_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, winner);
     TDK_CUDA(cudaGetLastError());
     age_gather_kernel<<<grid, TPB, 0, st>>>(age0, winner, hw, age1);
     TDK_CUDA(cudaGetLastError());
@@ -477,7 +525,8 @@ int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1,
     const size_t m = (n + SCAN_TILE - 1) / SCAN_TILE;
     TDK_CUDA(cudaMemsetAsync(cnt, 0, n * 4, st));
     dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
-    prop_count_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, tgt, cnt);
+    dim3 tgrid((unsigned)((W + RT_W - 1) / RT_W), (unsigned)((H + RT_H - 1) / RT_H), (unsigned)P);
+    prop_count_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, tgt, cnt);
     TDK_CUDA(cudaGetLastError());
     scan_sums_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum);
     TDK_CUDA(cudaGetLastError());
