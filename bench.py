@@ -280,6 +280,20 @@ def run_b200(args, rank, world, local_rank):
     ms_total = ev0.elapsed_time(ev1)
     sampler.join(timeout=1.0)
 
+    # ---- latency of ONE keyframe (8 references) per launch: "ms per keyframe-pair" without batching
+    one = {k: t[k][:1].contiguous() for k in names}
+    one_out = tuple(o[:1].contiguous() for o in out)
+    lat0, lat1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(5):
+        device.update_depth(*(one[k] for k in names), params, check=False, out=one_out, fuse=True)
+    torch.cuda.synchronize()
+    lat0.record()
+    for _ in range(50):
+        device.update_depth(*(one[k] for k in names), params, check=False, out=one_out, fuse=True)
+    lat1.record()
+    torch.cuda.synchronize()
+    single_ms = lat0.elapsed_time(lat1) / 50
+
     # ---- e2e: host-pointer C-ABI call, pinned host buffers, copies inside the timed region
     e2e_steps = args.e2e_steps or min(args.steps, 10)
     h_out = (torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
@@ -353,7 +367,7 @@ def run_b200(args, rank, world, local_rank):
             "l2": f"inputs {h2d / 1e9:.2f} GB per step >> 126 MB L2 (no flush needed)",
             "success_px_per_step": n_success, "success_px_per_s": world * n_success / (ms_step * 1e-3),
             "params": [float(x) for x in params], "e2e_matches_resident": same,
-            "nccl_gather_ms": gather_ms,
+            "nccl_gather_ms": gather_ms, "single_keyframe_launch_ms": single_ms,
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

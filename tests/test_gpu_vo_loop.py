@@ -79,3 +79,36 @@ def test_keyframe_loop_matches_oracle_frame_by_frame():
         poses.append(T_w1)
     assert updated > 100, "the sequence never produced a successful update"
     assert int(o_age.max()) >= 3
+
+
+def test_mapper_runs_the_same_loop():
+    """tadataka_b200.mapper.SemiDenseMapper == the hand-written loop above == the oracle."""
+    from rust_bindings.camera import CameraParameters
+    from tadataka_b200.mapper import SemiDenseMapper
+    H, W, n_frames = 96, 128, 6
+    cam = np.array([100.0, 100.0, 63.5, 47.5])
+    frames, cam, params = scene.make_sequence(3100, n_frames=n_frames, H=H, W=W, cam=cam)
+    oparams = ora.make_params(*params)
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    rng = np.random.default_rng(3100)
+    depth0 = rng.uniform(params[0], params[1], (H, W))
+    m = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0,
+                        fuse=False, regularize=False)
+    o_depth, o_var, o_age = depth0.copy(), np.full((H, W), 100.0), np.zeros((H, W), dtype=np.uint64)
+    refs, poses = [frames[0][0]], [frames[0][1]]
+    for i in range(1, n_frames):
+        img1, T_w1, _ = frames[i]
+        T10 = np.linalg.inv(T_w1) @ poses[-1]
+        o_age = ora.increment_age(o_age, cam, cam, T10, o_depth)
+        d1, v1 = ora.propagate(T10, cam, cam, o_depth, o_var, 200.0, 100.0, 1e-6)
+        R = len(refs)
+        o_depth, o_var, o_f = ora.update_depth(img1, cam, T_w1, np.stack(refs), np.tile(cam, (R, 1)),
+                                               np.stack(poses), o_age, d1, v1, oparams)
+        refs.append(img1)
+        poses.append(T_w1)
+        f = m.track(cp, img1, T_w1)
+        depth, var, age, flag = m.maps()
+        assert np.array_equal(flag, o_f) and np.array_equal(f.cpu().numpy(), o_f)
+        assert np.array_equal(depth, o_depth) and np.array_equal(var, o_var)
+        assert np.array_equal(age, o_age)
+    assert m.n_frames == n_frames
