@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--distinct", type=int, default=8, help="distinct rendered scenes per GPU")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 measurement")
     ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (0 two kernels, 1 one kernel)")
     return ap.parse_args()
 
@@ -294,6 +295,25 @@ def run_b200(args, rank, world, local_rank):
     torch.cuda.synchronize()
     single_ms = lat0.elapsed_time(lat1) / 50
 
+    # ---- secondary shape (BASELINE.json configs[3] "C4"): 1280x720 TUM-scale pairs, kernel only
+    c4_ms = None
+    if rank == 0 and not args.no_c4:
+        from tadataka_b200 import scene
+        c4 = scene.stack_keyframes([scene.make_pair(4000 + i, H=720, W=1280, cam=scene.CAM_720P,
+                                                    pset=scene.SET_T) for i in range(8)])
+        c4t = {k: torch.from_numpy(c4[k]).to(dev) for k in names}
+        c4p = np.ascontiguousarray(c4["params"], dtype=np.float64)
+        for _ in range(3):
+            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True)
+        torch.cuda.synchronize()
+        lat0.record()
+        for _ in range(10):
+            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True)
+        lat1.record()
+        torch.cuda.synchronize()
+        c4_ms = lat0.elapsed_time(lat1) / 10 / 8
+        del c4t
+
     # ---- e2e: host-pointer C-ABI call, pinned host buffers, copies inside the timed region
     e2e_steps = args.e2e_steps or min(args.steps, 10)
     h_out = (torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
@@ -368,6 +388,7 @@ def run_b200(args, rank, world, local_rank):
             "success_px_per_step": n_success, "success_px_per_s": world * n_success / (ms_step * 1e-3),
             "params": [float(x) for x in params], "e2e_matches_resident": same,
             "nccl_gather_ms": gather_ms, "single_keyframe_launch_ms": single_ms,
+            "c4_720p_ms_per_pair": c4_ms,
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -388,8 +409,9 @@ def run_b200(args, rank, world, local_rank):
         threads = host_threads()
         n_kf = min(B, max(threads, 8))
         v, best, reps = time_cpu(ora, b, n_kf, threads)
+        v1, _, _ = time_cpu(ora, b, 2, 1, budget_s=3.0, max_reps=3)
         line["cpu_baseline"] = {
-            "value": v, "unit": UNIT, "cores": threads, "kind": "port",
+            "value": v, "unit": UNIT, "cores": threads, "kind": "port", "single_thread_value": v1,
             "sample": f"{n_kf} of the step's {B} keyframes, best of {reps} runs, "
                       f"{1e3 * best / n_kf:.2f} ms/keyframe, OpenMP over keyframes"}
     print(json.dumps(line), flush=True)
