@@ -120,18 +120,6 @@ __device__ __forceinline__ int warp_target_n(const FrameConst &c, double qx, dou
     return (int)v * W + (int)u;
 }
 
-__device__ __forceinline__ int warp_target(const FrameConst &c, int x0, int y0, double depth0, int H,
-                                           int W, double &depth1)
-{
-    const double qx = ((double)x0 - c.o0x) / c.f0x;
-    const double qy = ((double)y0 - c.o0y) / c.f0y;
-    double x1, y1;
-    tdk::warp_point(c.T, qx, qy, depth0, x1, y1, depth1);
-    const double u = x1 * c.f1x + c.o1x;
-    const double v = y1 * c.f1y + c.o1y;
-    if (!tdk::in_range(u, v, (double)W - 1., (double)H - 1.)) return -1;
-    return (int)v * W + (int)u;
-}
 
 // ----------------------------------------------------------------------------- increment_age
 // age.rs:6-32.  The raster-order "last writer wins" becomes: the winner of a target is the source
@@ -190,8 +178,11 @@ __global__ void __launch_bounds__(TPB) age_gather_kernel(const uint64_t *__restr
 __global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restrict__ T10,
                                                          const double *__restrict__ cam0,
                                                          const double *__restrict__ cam1,
-                                                         const double *__restrict__ depth0, int H, int W,
-                                                         int *__restrict__ tgt, unsigned int *__restrict__ cnt)
+                                                         const double *__restrict__ depth0,
+                                                         const double *__restrict__ variance0, double bias,
+                                                         int H, int W, int *__restrict__ tgt,
+                                                         unsigned int *__restrict__ cnt, double *__restrict__ src_d1,
+                                                         double *__restrict__ src_v1)
 {
     __shared__ double s_qx[RT_W], s_qy[RT_H];
     const int p = blockIdx.z;
@@ -200,10 +191,17 @@ __global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restric
     int x, y;
     double qx, qy, d1;
     if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
-    const int s = y * W + x;
-    const int t = warp_target_n(c, qx, qy, depth0[(size_t)p * hw + s], H, W, d1);
-    tgt[(size_t)p * hw + s] = t;
-    if (t >= 0) atomicAdd(cnt + (size_t)p * hw + t, 1u);
+    const size_t s = (size_t)p * hw + (size_t)y * W + x;
+    const double d0 = depth0[s];
+    const int t = warp_target_n(c, qx, qy, d0, H, W, d1);
+    tgt[s] = t;
+    if (t < 0) return;
+    atomicAdd(cnt + (size_t)p * hw + t, 1u);
+    // what this source carries to its target: propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
+    const double ratio = tdk::inv(d1) / tdk::inv(d0);
+    const double r2 = ratio * ratio;
+    src_d1[s] = d1;
+    src_v1[s] = (r2 * r2) * variance0[s] + bias;
 }
 
 // exclusive scan of n u32 values, 1024 per block: (a) block sums, (b) scan of the sums by one
@@ -324,18 +322,14 @@ __device__ __forceinline__ void sift_down(unsigned int *a, unsigned int start, u
     }
 }
 
-__global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict__ T10,
-                                                        const double *__restrict__ cam0,
-                                                        const double *__restrict__ cam1,
-                                                        const double *__restrict__ depth0,
-                                                        const double *__restrict__ variance0, int H, int W,
+__global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict__ src_d1,
+                                                        const double *__restrict__ src_v1, int hw,
                                                         const unsigned int *__restrict__ off,
                                                         unsigned int *__restrict__ list, double def_d,
-                                                        double def_v, double bias, double *__restrict__ depth1,
+                                                        double def_v, double *__restrict__ depth1,
                                                         double *__restrict__ variance1)
 {
     const int p = blockIdx.y;
-    const int hw = H * W;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= hw) return;
     const size_t g = (size_t)p * hw + t;
@@ -364,17 +358,10 @@ __global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict
             }
         }
     }
-    const FrameConst c = load_frame_const(T10, cam0, cam1, p);
     double acc_d = 0., acc_v = 0.;
     for (unsigned int i = 0; i < k; i++) {
         const unsigned int s = seg[i];
-        const double d0 = depth0[(size_t)p * hw + s], v0 = variance0[(size_t)p * hw + s];
-        double d1a;
-        warp_target(c, (int)(s % W), (int)(s / W), d0, H, W, d1a);
-        // propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
-        const double ratio = tdk::inv(d1a) / tdk::inv(d0);
-        const double r2 = ratio * ratio;
-        const double v1a = (r2 * r2) * v0 + bias;
+        const double d1a = src_d1[(size_t)p * hw + s], v1a = src_v1[(size_t)p * hw + s];
         if (i == 0) { acc_d = d1a; acc_v = v1a; continue; }
         // handle_collision(a = new, b = stored), propagation.rs:21-46 ; stat.rs:5-26 ; fusion.rs:3-11
         const double ia = tdk::inv(d1a), ib = tdk::inv(acc_d);
@@ -397,7 +384,7 @@ __global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict
 size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 
 struct PropLayout {
-    size_t tgt, cnt, off, list, bsum, total;
+    size_t tgt, cnt, off, list, bsum, src_d1, src_v1, total;
 };
 PropLayout prop_layout(int64_t P, int64_t H, int64_t W)
 {
@@ -410,6 +397,8 @@ PropLayout prop_layout(int64_t P, int64_t H, int64_t W)
     l.off = o; o = up256(o + (n + 1) * 4);
     l.list = o; o = up256(o + n * 4);
     l.bsum = o; o = up256(o + (m + 1) * 4);
+    l.src_d1 = o; o = up256(o + n * 8);
+    l.src_v1 = o; o = up256(o + n * 8);
     l.total = o;
     return l;
 }
@@ -526,7 +515,9 @@ int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1,
     TDK_CUDA(cudaMemsetAsync(cnt, 0, n * 4, st));
     dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
     dim3 tgrid((unsigned)((W + RT_W - 1) / RT_W), (unsigned)((H + RT_H - 1) / RT_H), (unsigned)P);
-    prop_count_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, tgt, cnt);
+    double *src_d1 = (double *)(ws + l.src_d1), *src_v1 = (double *)(ws + l.src_v1);
+    prop_count_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, variance0, uncertaintity_bias, (int)H, (int)W,
+                                             tgt, cnt, src_d1, src_v1);
     TDK_CUDA(cudaGetLastError());
     scan_sums_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum);
     TDK_CUDA(cudaGetLastError());
@@ -536,8 +527,7 @@ int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1,
     TDK_CUDA(cudaGetLastError());
     prop_fill_kernel<<<grid, TPB, 0, st>>>(tgt, cnt, off, hw, list);
     TDK_CUDA(cudaGetLastError());
-    prop_fold_kernel<<<grid, TPB, 0, st>>>(T10, cam0, cam1, depth0, variance0, (int)H, (int)W, off, list,
-                                           default_depth, default_variance, uncertaintity_bias, depth1,
+    prop_fold_kernel<<<grid, TPB, 0, st>>>(src_d1, src_v1, hw, off, list, default_depth, default_variance, depth1,
                                            variance1);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
