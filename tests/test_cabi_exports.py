@@ -79,3 +79,43 @@ def test_frame_and_params_constructors():
         focal_length = np.array([1., 2.])
         offset = np.array([3., 4.])
     assert Frame(Duck(), np.zeros((4, 4)), np.eye(4)).camera_params.offset.tolist() == [3., 4.]
+
+
+def test_argument_errors_are_raised_before_any_cuda_call():
+    """Exact-dtype and shape checks of the drop-in layer (pyo3-numpy never casts:
+    src/py/semi_dense.rs:38-43,158-166); these fire before the GPU is touched."""
+    import numpy as np
+    import pytest
+    from rust_bindings.camera import CameraParameters
+    from rust_bindings.semi_dense import (Frame, Params, estimate_debug_, increment_age, propagate,
+                                          update_depth)
+    import rust_bindings.warp as rw
+    cp = CameraParameters((10., 10.), (8., 6.))
+    frame = Frame(cp, np.zeros((12, 16)), np.eye(4))
+    params = Params(0.1, 10.0, 0.4, 0.5, 0.02, 0.001)
+    age, d, v = np.ones((12, 16), dtype=np.uint64), np.ones((12, 16)), np.ones((12, 16))
+    with pytest.raises(TypeError):
+        update_depth(frame, [frame], age.astype(np.int64), d, v, params)       # age must be uint64
+    with pytest.raises(TypeError):
+        update_depth(frame, [frame], age, d.astype(np.float32), v, params)
+    with pytest.raises(TypeError):
+        update_depth(frame, [object()], age, d, v, params)                      # not a Frame
+    with pytest.raises(TypeError):
+        update_depth(frame, [frame], age, d, v, (0.1, 10.0, 0.4, 0.5, 0.02, 0.001))
+    with pytest.raises(ValueError):
+        update_depth(frame, [frame], age[:5], d, v, params)                     # shape mismatch
+    with pytest.raises(ValueError):
+        update_depth(frame, [Frame(cp, np.zeros((6, 16)), np.eye(4))], age, d, v, params)
+    with pytest.raises(TypeError):
+        estimate_debug_(np.array([1., 2.]), 1.0, 1.0, frame, frame, params)     # u_key must be int64
+    with pytest.raises(TypeError):
+        increment_age(age.astype(np.int32), cp, cp, np.eye(4), d)
+    with pytest.raises(TypeError):
+        propagate(np.eye(4, dtype=np.float32), cp, cp, d, v, 1.0, 1.0, 0.1)
+    with pytest.raises(TypeError):
+        rw.warp_vecs(np.eye(4), np.zeros((3, 2), dtype=np.float32), np.ones(3))
+    # no reference frames: every pixel must be age 0, and comes back unprocessed
+    out_d, out_v, out_f = update_depth(frame, [], np.zeros((12, 16), dtype=np.uint64), d, v, params)
+    assert (out_f == -9).all() and np.array_equal(out_d, d)
+    with pytest.raises(ValueError, match="Age exceeds"):
+        update_depth(frame, [], age, d, v, params)
