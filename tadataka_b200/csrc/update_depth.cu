@@ -207,7 +207,7 @@ struct CtaQueue {
     unsigned short ref[BLOCK], owner[BLOCK];  // reference index; slot of the owning thread (one-kernel plan)
 };
 
-constexpr size_t CTA_DYN_SMEM = sizeof(CtaQueue);
+constexpr size_t CTA_SMEM_BYTES = sizeof(CtaQueue);   // dynamic shared memory of the tile and search kernels
 
 struct A1Result {
     double ki[5];
@@ -790,7 +790,7 @@ WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W)
 
 enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1 };
 int g_plan = PLAN_TWO_KERNELS;
-constexpr size_t FLAT_DYN_SMEM = CTA_DYN_SMEM;
+
 
 int launch(const double *key_imgs, const double *const *key_ptrs_host, const double *key_cams,
            const double *T_wk, const double *ref_imgs, const double *const *ref_ptrs_host,
@@ -865,14 +865,14 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     TDK_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
         TDK_CUDA(cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)FLAT_DYN_SMEM));
+                                      (int)CTA_SMEM_BYTES));
         TDK_CUDA(cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)FLAT_DYN_SMEM));
+                                      (int)CTA_SMEM_BYTES));
         attr_set[dev] = true;
     }
     if (plan == PLAN_ONE_KERNEL) {
         a.cand = nullptr; a.cand_count = nullptr;
-        update_depth_tile_kernel<<<grid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+        update_depth_tile_kernel<<<grid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
     } else {
         a.cand_count = (unsigned int *)(ws + l.cand_count);
         a.cand = (unsigned int *)(ws + l.cand);
@@ -880,7 +880,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
         TDK_CUDA(cudaGetLastError());
         const dim3 sgrid((unsigned)((tiles_x * tiles_y + 3) / 4), 1u, (unsigned)P);
-        update_depth_search_kernel<<<sgrid, BLOCK, FLAT_DYN_SMEM, stream>>>(a);
+        update_depth_search_kernel<<<sgrid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
