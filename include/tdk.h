@@ -222,6 +222,42 @@ int tdk_transform_dev(const double *T10, const double *ps0, int64_t n, double *p
 int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1, int64_t n,
                         double *depths0, void *stream);
 
+/* ------------------------------------------------------------------ direct pose-change estimation
+ * The caller on the other side of the keyframe loop: tadataka/vo/dvo/__init__.py.
+ * One Gauss-Newton iteration of _PoseChangeEstimator.__call__ (:76-110) = one
+ * tdk_dvo_normal_equations_dev (calc_pose_update, :46-73, with calc_jacobian of
+ * tadataka/vo/dvo/jacobian.py:8-24) + one tdk_dvo_photometric_error_dev (tadataka/metric.py:13-39);
+ * the 6x6 solve, the SE(3) exponential and the loop stay on the host (tadataka_b200/dvo.py).
+ * Images, depth map, gradients, weights: device [H,W] f64.  cam0, cam1 (4 doubles each) and T10
+ * (16 doubles, frame 1 <- frame 0) are HOST pointers, passed to the kernels by value.
+ *
+ * tdk_image_gradient_dev: np.gradient as calc_image_gradient uses it (jacobian.py:27-29) -> (DX, DY).
+ *
+ * tdk_dvo_normal_equations_dev: out = 30 device doubles: [0..20] upper triangle of J^T W J (row-major:
+ *   00 01 .. 05 11 12 ..), [21..26] J^T W r, [27] number of pixels used, [28] sum w r^2, [29] sum r^2,
+ *   over the pixels whose warped position lies inside image 1 and in front of camera 1; r = I0 - I1 at
+ *   the SAME pixel, as the reference computes it (:90).  weight_mode: 0 none, 1 `weights` map
+ *   (:71-72), 2 Huber with k = weight_param (robust/weights.py:38-43), 3 Student-t with
+ *   variance = weight_param and nu (robust/weights.py:4-20; find the variance with
+ *   tdk_dvo_student_t_dev).  Tukey weights need a median and are not provided.
+ * tdk_dvo_student_t_dev: out = {sum of r^2 (nu+1)/(nu + r^2/variance), count} over the same pixels:
+ *   one step of the variance fixed point of compute_weights_student_t.
+ * tdk_dvo_photometric_error_dev: out = {sum (I0 - I1(warp))^2, count} over the pixels whose warped
+ *   position lies inside image 1 (no depth-sign test, metric.py:22). */
+int tdk_image_gradient_dev(const double *image, int64_t H, int64_t W, double *gx, double *gy,
+                           void *stream);
+int tdk_dvo_normal_equations_dev(const double *I0, const double *D0, const double *I1,
+                                 const double *GX1, const double *GY1, const double *weights,
+                                 int weight_mode, double weight_param, double nu, const double *cam0,
+                                 const double *cam1, const double *T10, int64_t H, int64_t W,
+                                 double *out, void *stream);
+int tdk_dvo_student_t_dev(const double *I0, const double *D0, const double *I1, double variance,
+                          double nu, const double *cam0, const double *cam1, const double *T10,
+                          int64_t H, int64_t W, double *out, void *stream);
+int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const double *I1,
+                                  const double *cam0, const double *cam1, const double *T10,
+                                  int64_t H, int64_t W, double *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,13 @@ inv_project_vecs_dev = _sig("tdk_inv_project_vecs_dev", C.c_int, P, P, I64, P, P
 transform_dev = _sig("tdk_transform_dev", C.c_int, P, P, I64, P, P)
 calc_depth0_dev = _sig("tdk_calc_depth0_dev", C.c_int, P, P, P, I64, P, P)
 
+image_gradient_dev = _sig("tdk_image_gradient_dev", C.c_int, P, I64, I64, P, P, P)
+dvo_normal_equations_dev = _sig("tdk_dvo_normal_equations_dev", C.c_int, P, P, P, P, P, P, C.c_int, D, D,
+                                P, P, P, I64, I64, P, P)
+dvo_student_t_dev = _sig("tdk_dvo_student_t_dev", C.c_int, P, P, P, D, D, P, P, P, I64, I64, P, P)
+dvo_photometric_error_dev = _sig("tdk_dvo_photometric_error_dev", C.c_int, P, P, P, P, P, P, I64, I64, P,
+                                 P)
+
 # every symbol include/tdk.h declares (tests check the header against this list and the .so)
 EXPORTS = [
     "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
@@ -73,6 +80,8 @@ EXPORTS = [
     "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",
     "tdk_propagate_dev", "tdk_warp_vecs_dev", "tdk_interpolate_dev", "tdk_project_vecs_dev",
     "tdk_inv_project_vecs_dev", "tdk_transform_dev", "tdk_calc_depth0_dev",
+    "tdk_image_gradient_dev", "tdk_dvo_normal_equations_dev", "tdk_dvo_student_t_dev",
+    "tdk_dvo_photometric_error_dev",
 ]
 
 

@@ -1,0 +1,223 @@
+"""Direct (photometric) pose-change estimation on the GPU: the reference's
+`tadataka.vo.dvo.PoseChangeEstimator` (tadataka/vo/dvo/__init__.py:76-150), the caller on the other
+side of the semi-dense keyframe loop (examples/semi_dense_vo.py:45-54 feeds it the depth and
+variance maps `update_depth` produces).
+
+Per Gauss-Newton iteration the two per-pixel passes -- building J^T W J / J^T W r
+(calc_pose_update, :46-73) and re-evaluating the photometric error (tadataka/metric.py:13-39) --
+run as CUDA reductions (csrc/dvo.cu behind include/tdk.h); 30 + 2 doubles come back per iteration
+and the 6x6 solve, the SE(3) exponential (tadataka/se3.py:16-31) and the accept/stop rule
+(:98-108) run on the host.  Poses are 4x4 matrices T10 (frame 1 <- frame 0) instead of the
+reference's `Pose` objects.
+
+Deviations from the reference:
+  * the least-squares step solves the 6x6 normal equations (minimum-norm, via lstsq) instead of
+    running lstsq on the [N,6] system (tadataka/math.py:34-50): same minimiser, different rounding;
+  * the image pyramid (:139-148) uses `rescale` below (Gaussian pre-filter + bilinear), not
+    skimage.transform.rescale, which is not available here;
+  * weights="tukey" (median based) is not provided on the device.
+"""
+import ctypes as C
+import warnings
+
+import numpy as np
+import torch
+from scipy.ndimage import gaussian_filter, map_coordinates
+from scipy.spatial.transform import Rotation
+
+from . import _lib, device
+from .camera import camera_vector
+
+_F64 = torch.float64
+HUBER_K = 1.345       # tadataka/robust/weights.py:38
+STUDENT_NU = 5.0      # tadataka/robust/weights.py:4
+STUDENT_ITERS = 10
+
+
+def _vp(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _dev(a):
+    if isinstance(a, torch.Tensor):
+        return device._chk(a, "image", _F64)
+    a = np.ascontiguousarray(a)
+    if a.dtype != np.float64 or a.ndim != 2:
+        raise TypeError("images and maps must be 2-D float64")
+    device._require_cuda()
+    return torch.from_numpy(a).cuda()
+
+
+def tangent_so3(v):
+    return np.array([[0., -v[2], v[1]], [v[2], 0., -v[0]], [-v[1], v[0], 0.]])
+
+
+def exp_se3(xi):
+    """4x4 matrix of the twist xi = (v, rotvec): tadataka/pose.py:44-46 + tadataka/se3.py:16-31."""
+    v, rotvec = xi[:3], xi[3:]
+    theta = np.linalg.norm(rotvec)
+    omega = np.zeros(3) if theta == 0 else rotvec / theta
+    K = tangent_so3(omega)
+    I = np.eye(3)
+    if theta < 1e-16:
+        V = I + K * theta / 2 + np.dot(K, K) * pow(theta, 2) / 6
+    else:
+        V = I + (1 - np.cos(theta)) / theta * K + (theta - np.sin(theta)) / theta * np.dot(K, K)
+    T = np.eye(4)
+    T[:3, :3] = Rotation.from_rotvec(rotvec).as_matrix()
+    T[:3, 3] = np.dot(V, v)
+    return T
+
+
+def image_gradient(image):
+    """(DX, DY) = np.gradient along x and y (tadataka/vo/dvo/jacobian.py:27-29), device tensors."""
+    image = _dev(image)
+    H, W = image.shape
+    gx, gy = torch.empty_like(image), torch.empty_like(image)
+    _lib.check(_lib.image_gradient_dev(device._ptr(image), H, W, device._ptr(gx), device._ptr(gy),
+                                       device._stream()))
+    return gx, gy
+
+
+class _Level:
+    """Device-resident inputs of one pyramid level."""
+
+    def __init__(self, cam0, cam1, I0, D0, I1, W0=None):
+        self.cam0 = np.ascontiguousarray(cam0, dtype=np.float64)
+        self.cam1 = np.ascontiguousarray(cam1, dtype=np.float64)
+        self.I0, self.D0, self.I1 = _dev(I0), _dev(D0), _dev(I1)
+        if not (self.I0.shape == self.D0.shape == self.I1.shape):
+            raise ValueError("I0, D0 and I1 must have the same shape")
+        self.W0 = _dev(W0) if W0 is not None else None
+        if self.W0 is not None and self.W0.shape != self.I0.shape:
+            raise ValueError("the weight map must have the image's shape")
+        self.H, self.W = self.I0.shape
+        self.GX1, self.GY1 = image_gradient(self.I1)
+        self.acc = torch.empty(32, dtype=_F64, device=self.I0.device)
+
+    def photometric_error(self, T10):
+        T10 = np.ascontiguousarray(T10, dtype=np.float64)
+        _lib.check(_lib.dvo_photometric_error_dev(
+            device._ptr(self.I0), device._ptr(self.D0), device._ptr(self.I1), _vp(self.cam0),
+            _vp(self.cam1), _vp(T10), self.H, self.W, device._ptr(self.acc), device._stream()))
+        s, n = self.acc[:2].cpu().numpy()
+        return s / n if n > 0 else np.nan      # np.mean of an empty array is nan, as in metric.py
+
+    def _student_t_variance(self, T10):
+        variance = 1.0
+        for _ in range(STUDENT_ITERS):
+            _lib.check(_lib.dvo_student_t_dev(
+                device._ptr(self.I0), device._ptr(self.D0), device._ptr(self.I1), variance, STUDENT_NU,
+                _vp(self.cam0), _vp(self.cam1), _vp(T10), self.H, self.W, device._ptr(self.acc),
+                device._stream()))
+            s, n = self.acc[:2].cpu().numpy()
+            if n == 0:
+                return None
+            variance = s / n
+        return variance
+
+    def normal_equations(self, T10, weights):
+        """-> (A [6,6], b [6], n_used) of calc_pose_update, or None if no pixel is usable."""
+        T10 = np.ascontiguousarray(T10, dtype=np.float64)
+        mode, param, wmap = 0, 0.0, None
+        if weights is None:
+            pass
+        elif isinstance(weights, str):
+            if weights == "huber":
+                mode, param = 2, HUBER_K
+            elif weights == "student-t":
+                mode, param = 3, self._student_t_variance(T10)
+                if param is None:
+                    return None
+            elif weights == "tukey":
+                raise NotImplementedError("tukey weights need a device median; use 'huber' or 'student-t'")
+            else:
+                raise ValueError(f"No such weights '{weights}'")
+        else:
+            mode, wmap = 1, self.W0
+        _lib.check(_lib.dvo_normal_equations_dev(
+            device._ptr(self.I0), device._ptr(self.D0), device._ptr(self.I1), device._ptr(self.GX1),
+            device._ptr(self.GY1), device._ptr(wmap), mode, float(param), STUDENT_NU, _vp(self.cam0),
+            _vp(self.cam1), _vp(T10), self.H, self.W, device._ptr(self.acc), device._stream()))
+        acc = self.acc[:30].cpu().numpy()
+        if acc[27] == 0:
+            return None
+        A = np.zeros((6, 6))
+        A[np.triu_indices(6)] = acc[:21]
+        A = A + np.triu(A, 1).T
+        return A, acc[21:27].copy(), int(acc[27])
+
+
+def estimate_pose_change(camera_params0, camera_params1, I0, D0, I1, T10=None, weights=None,
+                         max_iter=20, trace=None):
+    """_PoseChangeEstimator.__call__ (tadataka/vo/dvo/__init__.py:76-110) at one resolution.
+    I0, D0, I1 (and a weight map) are float64 [H,W] numpy arrays or CUDA tensors; returns T10."""
+    cam0 = camera_params0 if isinstance(camera_params0, np.ndarray) else camera_vector(camera_params0)
+    cam1 = camera_params1 if isinstance(camera_params1, np.ndarray) else camera_vector(camera_params1)
+    wmap = None if weights is None or isinstance(weights, str) else weights
+    level = _Level(cam0, cam1, I0, D0, I1, wmap)
+    return _iterate(level, np.eye(4) if T10 is None else np.array(T10, dtype=np.float64), weights,
+                    max_iter, trace)
+
+
+def _iterate(level, T10, weights, max_iter, trace=None):
+    prev_error = level.photometric_error(T10)
+    for _ in range(max_iter):
+        ne = level.normal_equations(T10, weights)
+        if ne is None:
+            warnings.warn("Camera pose change is too large.", RuntimeWarning)
+            return T10
+        A, b, _ = ne
+        xi = np.linalg.lstsq(A, b, rcond=None)[0]
+        candidate = exp_se3(xi) @ T10                  # pose.py:51-53: dpose * pose10
+        curr_error = level.photometric_error(candidate)
+        if trace is not None:
+            trace.append((xi, curr_error))
+        if curr_error > prev_error:
+            break
+        prev_error = curr_error
+        T10 = candidate
+    return T10
+
+
+def rescale(image, scale):
+    """Anti-aliased bilinear resampling by `scale` (<= 1).  Stands in for skimage.transform.rescale
+    (tadataka/vo/dvo/__init__.py:143-148); NOT numerically identical to it."""
+    image = np.asarray(image, dtype=np.float64)
+    if scale == 1:
+        return image.copy()
+    H, W = image.shape
+    h, w = int(round(H * scale)), int(round(W * scale))
+    sigma = max(0.0, (1.0 / scale - 1.0) / 2.0)
+    smooth = gaussian_filter(image, sigma, mode="reflect") if sigma > 0 else image
+    ys = (np.arange(h) + 0.5) / scale - 0.5
+    xs = (np.arange(w) + 0.5) / scale - 0.5
+    yy, xx = np.meshgrid(ys, xs, indexing="ij")
+    return map_coordinates(smooth, [yy, xx], order=1, mode="reflect")
+
+
+class PoseChangeEstimator:
+    """`PoseChangeEstimator(camera_params0, camera_params1, n_coarse_to_fine=5, max_iter=20,
+    layer_size_ratio=1.5)`; call it with `(I0, D0, I1, weights=None, pose10=identity)`
+    (tadataka/vo/dvo/__init__.py:113-150).  camera_params*: objects with .focal_length / .offset."""
+
+    def __init__(self, camera_params0, camera_params1, n_coarse_to_fine=5, max_iter=20,
+                 layer_size_ratio=1.5):
+        self.cam0 = camera_vector(camera_params0)
+        self.cam1 = camera_vector(camera_params1)
+        self.n_coarse_to_fine = n_coarse_to_fine
+        self.max_iter = max_iter
+        self.layer_size_ratio = layer_size_ratio
+
+    def __call__(self, I0, D0, I1, weights=None, pose10=None):
+        I0, D0, I1 = (np.asarray(a, dtype=np.float64) for a in (I0, D0, I1))
+        if not (I0.shape == D0.shape == I1.shape) or I0.ndim != 2:
+            raise ValueError("I0, D0, I1 must be 2-D arrays of one shape")
+        T10 = np.eye(4) if pose10 is None else np.array(pose10, dtype=np.float64)
+        for level in reversed(range(self.n_coarse_to_fine)):
+            scale = 1 / pow(self.layer_size_ratio, level)      # level_to_scale, :42-43
+            W0 = rescale(weights, scale) if isinstance(weights, np.ndarray) else None
+            lv = _Level(self.cam0 * scale, self.cam1 * scale, rescale(I0, scale), rescale(D0, scale),
+                        rescale(I1, scale), W0)                # camera.resize, camera/model.py:69-74
+            T10 = _iterate(lv, T10, weights, self.max_iter)
+        return T10

@@ -1,0 +1,113 @@
+"""GPU parity of the direct pose-change estimator (tadataka_b200.dvo, csrc/dvo.cu) against the
+numpy restatement of tadataka/vo/dvo (oracle/dvo.py).  The sums are floating-point reductions in
+another order than numpy's, so the comparisons are to a stated tolerance, not bit for bit:
+    counts and the image gradient      exact
+    J^T W J, J^T W r, error sums       1e-10 relative (to the largest entry)
+    pose after the full iteration      1e-7 absolute on the 4x4
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle as ora
+from oracle import dvo as odvo
+from tadataka_b200 import scene
+
+pytestmark = pytest.mark.gpu
+RTOL_SUMS = 1e-10
+ATOL_POSE = 1e-7
+
+
+def _pair(seed=9000, H=96, W=128, t=(1.5, -0.6, 0.9), rot=(0.004, -0.006, 0.003)):
+    cam = np.array([110.0, 110.0, (W - 1) / 2.0, (H - 1) / 2.0])
+    world = scene.World(scene.SET_S, seed)
+    T_w1 = scene.pose(scene.rotation(*rot), t)
+    I0, D0 = world.render(scene.pose(), cam, H, W)
+    I1, _ = world.render(T_w1, cam, H, W)
+    return cam, I0, D0, I1, np.linalg.inv(T_w1)
+
+
+def _oracle_normal_equations(cam0, cam1, I0, D0, I1, T10, weights):
+    """J^T W J, J^T W r, count built the way calc_pose_update builds J, r and the weights."""
+    us0 = odvo.image_coordinates(I0.shape)
+    P0 = ora.inv_project_vecs(odvo.normalize(cam0, us0.astype(np.float64)), D0.flatten())
+    P1 = np.dot(T10[:3, :3], P0.T).T + T10[:3, 3]
+    GX1, GY1 = odvo.calc_image_gradient(I1)
+    us1 = odvo.unnormalize(cam1, ora.project_vecs(P1))
+    mask = odvo.is_in_image_range(us1, I0.shape) & (P1[:, 2] > 0)
+    r = (I0 - I1).flatten()[mask]
+    J = odvo.calc_jacobian(cam1[0:2], ora.interpolate(GX1, us1[mask]), ora.interpolate(GY1, us1[mask]),
+                           P1[mask])
+    if weights is None:
+        w = np.ones(r.shape)
+    elif isinstance(weights, str):
+        w = odvo.compute_weights(weights, r)
+    else:
+        w = weights.flatten()[mask]
+    return (J * w[:, None]).T @ J, (J * w[:, None]).T @ r, int(mask.sum())
+
+
+def test_image_gradient_is_numpy_gradient():
+    from tadataka_b200 import dvo
+    rng = np.random.default_rng(1)
+    for shape in [(13, 17), (4, 64), (97, 131), (2, 2)]:
+        img = rng.random(shape)
+        gx, gy = dvo.image_gradient(img)
+        DX, DY = odvo.calc_image_gradient(img)
+        assert np.array_equal(gx.cpu().numpy(), DX) and np.array_equal(gy.cpu().numpy(), DY)
+
+
+@pytest.mark.parametrize("weights", [None, "array", "huber", "student-t"])
+def test_normal_equations_and_error_match_oracle(weights):
+    from tadataka_b200 import dvo
+    cam, I0, D0, I1, T10_true = _pair()
+    rng = np.random.default_rng(2)
+    wmap = rng.uniform(0.2, 2.0, I0.shape) if weights == "array" else weights
+    level = dvo._Level(cam, cam, I0, D0, I1, wmap if isinstance(wmap, np.ndarray) else None)
+    for T10 in (np.eye(4), T10_true, scene.pose(scene.rotation(0.01, 0.02, -0.01), (3., 1., -2.))):
+        A, b, n = level.normal_equations(T10, wmap)
+        oA, ob, on = _oracle_normal_equations(cam, cam, I0, D0, I1, T10, wmap)
+        assert n == on
+        assert np.max(np.abs(A - oA)) <= RTOL_SUMS * np.max(np.abs(oA))
+        assert np.max(np.abs(b - ob)) <= RTOL_SUMS * np.max(np.abs(ob))
+        e, oe = level.photometric_error(T10), odvo.photometric_error(T10, cam, cam, I0, D0, I1)
+        assert abs(e - oe) <= RTOL_SUMS * oe
+
+
+@pytest.mark.parametrize("weights", [None, "huber", "student-t"])
+def test_single_level_estimator_follows_the_oracle(weights):
+    from tadataka_b200 import dvo
+    cam, I0, D0, I1, T10_true = _pair()
+    gtrace, otrace = [], []
+    T = dvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), weights, max_iter=20, trace=gtrace)
+    oT = odvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), weights, max_iter=20, trace=otrace)
+    assert len(gtrace) == len(otrace) and len(gtrace) >= 2
+    assert np.max(np.abs(T - oT)) <= ATOL_POSE
+    np.testing.assert_allclose(gtrace[0][0], otrace[0][0], rtol=1e-8, atol=1e-12)   # first update xi
+    # and it does what the reference's own test asks (tests/vo/test_dvo.py:33-44)
+    e_id = odvo.photometric_error(np.eye(4), cam, cam, I0, D0, I1)
+    e_true = odvo.photometric_error(T10_true, cam, cam, I0, D0, I1)
+    e = odvo.photometric_error(T, cam, cam, I0, D0, I1)
+    assert e < e_id and e < max(3.0 * e_true, 0.5 * e_id)
+
+
+def test_pyramid_estimator_and_error_cases():
+    from rust_bindings.camera import CameraParameters
+    from tadataka_b200 import dvo
+    cam, I0, D0, I1, T10_true = _pair(seed=9001, H=120, W=160, t=(4.0, -1.5, 2.0), rot=(0.01, -0.015, 0.008))
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    est = dvo.PoseChangeEstimator(cp, cp, n_coarse_to_fine=4, max_iter=20)
+    e_id = odvo.photometric_error(np.eye(4), cam, cam, I0, D0, I1)
+    e_true = odvo.photometric_error(T10_true, cam, cam, I0, D0, I1)
+    for weights in (None, np.ones(I0.shape), "huber", "student-t"):
+        T = est(I0, D0, I1, weights)
+        e = odvo.photometric_error(T, cam, cam, I0, D0, I1)
+        assert e < e_id, weights
+        assert e < max(2.0 * e_true, 0.25 * e_id), (weights, e, e_true, e_id)
+    with pytest.raises(ValueError, match="No such weights 'random'"):
+        est(I0, D0, I1, "random")
+    # a pose that throws every pixel out of the image: the reference warns and returns its input
+    far = scene.pose(None, (1e6, 0., 0.))
+    with pytest.warns(RuntimeWarning, match="too large"):
+        out = dvo.estimate_pose_change(cam, cam, I0, D0, I1, far, None, max_iter=3)
+    assert np.array_equal(out, far)

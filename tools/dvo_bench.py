@@ -1,0 +1,63 @@
+"""Times one Gauss-Newton iteration of the direct pose-change estimator at 640x480 (the two
+per-pixel passes of csrc/dvo.cu), against the HBM roofline and the numpy oracle on the host.
+    python tools/dvo_bench.py [--iters 50]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import dvo as odvo  # noqa: E402
+from tadataka_b200 import dvo, scene  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--iters", type=int, default=50)
+args = ap.parse_args()
+H, W = 480, 640
+try:
+    PEAK = float(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    PEAK = 6650.0
+cam = scene.CAM_VGA
+world = scene.World(scene.SET_S, 9100)
+T_w1 = scene.pose(scene.rotation(0.004, -0.006, 0.003), (1.5, -0.6, 0.9))
+I0, D0 = world.render(scene.pose(), cam, H, W)
+I1, _ = world.render(T_w1, cam, H, W)
+T10 = np.linalg.inv(T_w1)
+level = dvo._Level(cam, cam, I0, D0, I1)
+
+
+def timeit(fn):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / args.iters
+
+
+rows = [("normal equations (40 B/px: I0, I1, D0 + 2 gradient gathers)", 40, lambda: level.normal_equations(T10, None)),
+        ("normal equations, huber", 40, lambda: level.normal_equations(T10, "huber")),
+        ("photometric error (24 B/px: I0, D0 + I1 gather)", 24, lambda: level.photometric_error(T10))]
+print(f"{W}x{H}, HBM peak {PEAK} GB/s; times include the 240-byte result read-back (one sync per call)")
+for name, bpp, fn in rows:
+    ms = timeit(fn)
+    print(f"{name:66s} {ms * 1e3:8.1f} us  {bpp * H * W / ms / 1e6:7.1f} GB/s  {100 * bpp * H * W / ms / 1e6 / PEAK:5.1f}% of HBM peak")
+t0 = time.perf_counter()
+T = dvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), None, max_iter=20)
+torch.cuda.synchronize()
+t_gpu = time.perf_counter() - t0
+trace = []
+t0 = time.perf_counter()
+oT = odvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), None, max_iter=20, trace=trace)
+t_cpu = time.perf_counter() - t0
+print(f"full single-level estimate ({len(trace)} iterations): GPU {t_gpu * 1e3:.1f} ms, numpy oracle {t_cpu * 1e3:.1f} ms, "
+      f"max |dT| {np.max(np.abs(T - oT)):.2e}")
