@@ -55,74 +55,69 @@ def calc_image_gradient(image):
 
 
 def calc_jacobian(focal_length, didx, didy, P):
-    """tadataka/vo/dvo/jacobian.py:8-24"""
-    fx, fy = focal_length
-    fgx, fgy = fx * didx, fy * didy
-    x, y, z = P[:, 0], P[:, 1], P[:, 2]
-    z2 = z * z
-    xy = x * y
-    return np.column_stack((
-        fgx / z,
-        fgy / z,
-        -(fgx * x + fgy * y) / (z * z),
-        -(fgx * xy + fgy * (z2 + y * y)) / z2,
-        (fgx * (z2 + x * x) + fgy * xy) / z2,
-        (-fgx * y + fgy * x) / z
-    ))
+    """d(intensity)/d(twist) per point, [N,6]: Kerl's formula as tadataka/vo/dvo/jacobian.py:8-24
+    evaluates it (same operations in the same order, so the golden vectors match bit for bit)."""
+    a = focal_length[0] * didx          # fx * dI/dx
+    b = focal_length[1] * didy          # fy * dI/dy
+    X, Y, Z = P[:, 0], P[:, 1], P[:, 2]
+    ZZ = Z * Z
+    XY = X * Y
+    cols = [a / Z,
+            b / Z,
+            -(a * X + b * Y) / (Z * Z),
+            -(a * XY + b * (ZZ + Y * Y)) / ZZ,
+            (a * (ZZ + X * X) + b * XY) / ZZ,
+            (-a * Y + b * X) / Z]
+    return np.stack(cols, axis=1)
 
 
 # ---------------------------------------------------------------------------------- robust weights
 def compute_weights_student_t(r, nu=5, n_iter=10):
-    """tadataka/robust/weights.py:4-20 (returns the SQUARE ROOT of the t-weights)."""
-    s = np.power(r, 2)
-
-    def weights(variance):
-        return (nu + 1) / (nu + s / variance)
-
-    variance = 1.0
+    """tadataka/robust/weights.py:4-20: fixed point of the t-distribution scale, then the SQUARE
+    ROOT of the t-weights is what comes back."""
+    sq = np.power(r, 2)
+    var = 1.0
     for _ in range(n_iter):
-        variance = np.mean(s * weights(variance))
-    return np.sqrt(weights(variance))
+        var = np.mean(sq * ((nu + 1) / (nu + sq / var)))
+    return np.sqrt((nu + 1) / (nu + sq / var))
 
 
 def compute_weights_huber(r, k=1.345):
-    """tadataka/robust/weights.py:38-43"""
-    w = np.ones(r.shape)
-    a = np.abs(r)
-    m = a > k
-    w[m] = k / a[m]
-    return w
+    """tadataka/robust/weights.py:38-43: 1 inside the band, k/|r| outside."""
+    mag = np.abs(r)
+    out = np.ones(r.shape)
+    outside = mag > k
+    out[outside] = k / mag[outside]
+    return out
 
 
 def compute_weights_tukey(r, beta=4.6851, c=1.4826):
-    """tadataka/robust/weights.py:23-35"""
-    sigma = c * np.median(np.abs(r - np.median(r)))
-    x = r / sigma
-    w = np.zeros(x.shape)
-    m = np.abs(x) <= beta
-    w[m] = np.power(1 - np.power(x[m] / beta, 2), 2)
-    return w
+    """tadataka/robust/weights.py:23-35: biweight of r / (c * MAD)."""
+    mad = np.median(np.abs(r - np.median(r)))
+    u = r / (c * mad)
+    out = np.zeros(u.shape)
+    inside = np.abs(u) <= beta
+    out[inside] = np.power(1 - np.power(u[inside] / beta, 2), 2)
+    return out
+
+
+_WEIGHTS = {"tukey": compute_weights_tukey, "student-t": compute_weights_student_t,
+            "huber": compute_weights_huber}
 
 
 def compute_weights(name, residuals):
     """tadataka/vo/dvo/__init__.py:32-39"""
-    if name == "tukey":
-        return compute_weights_tukey(residuals)
-    if name == "student-t":
-        return compute_weights_student_t(residuals)
-    if name == "huber":
-        return compute_weights_huber(residuals)
-    raise ValueError(f"No such weights '{name}'")
+    if name not in _WEIGHTS:
+        raise ValueError(f"No such weights '{name}'")
+    return _WEIGHTS[name](residuals)
 
 
 def solve_linear_equation(A, b, weights=None):
-    """tadataka/math.py:34-50 with the default "lstsq" solver."""
+    """tadataka/math.py:34-50 with the default "lstsq" solver: rows scaled by sqrt(weights)."""
     if weights is not None:
-        w = np.sqrt(weights)
-        b = b * w
-        A = A * w.reshape(-1, 1)
-    x, _, _, _ = np.linalg.lstsq(A, b, rcond=None)
-    return x
+        root = np.sqrt(weights)
+        A, b = A * root[:, None], b * root
+    return np.linalg.lstsq(A, b, rcond=None)[0]
 
 
 # ---------------------------------------------------------------------------------- SE(3)
