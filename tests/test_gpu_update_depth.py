@@ -267,6 +267,45 @@ def test_fused_update_equals_update_then_fusion():
     assert np.all(want_v[ok] <= b["prior_variance"][ok])
 
 
+def test_full_size_c2_batch_properties():
+    """BASELINE.json configs[1] at the bench's full size (64 VGA keyframes x 8 references): too big
+    for the oracle in a test, so size-independent properties instead -- the two kernel plans (two
+    different kernels) agree bit for bit, a rerun is bit-identical, the flag histogram adds up to
+    the pixel count, failed pixels carry their prior -- plus the oracle on three keyframes of the
+    batch."""
+    import bench
+    from tadataka_b200 import _lib
+    b = bench.make_workload(0, 64, 8)
+    P, H, W = b["key_img"].shape
+    assert (P, H, W) == (64, 480, 640)
+    try:
+        _lib.set_kernel_plan(0)
+        a0 = _gpu(b, hist=True)
+        a1 = _gpu(b, hist=True)
+        _lib.set_kernel_plan(1)
+        c0 = _gpu(b, hist=True)
+    finally:
+        _lib.set_kernel_plan(0)
+    for x, y, z in zip(a0, a1, c0):
+        assert np.array_equal(x, y, equal_nan=True), "rerun differs"
+        assert np.array_equal(x, z, equal_nan=True), "kernel plans differ"
+    d, v, f, am, hist = a0
+    assert f.min() >= -9 and f.max() <= 0
+    assert int(hist.sum()) == P * H * W
+    assert [int(h) for h in hist.sum(0)] == [int((f == -k).sum()) for k in range(10)]
+    failed = f != 0
+    assert np.array_equal(v[failed], b["prior_variance"][failed])
+    untouched = (f == -9) | (f == -7) | (f == -1)
+    assert np.array_equal(d[untouched], b["prior_depth"][untouched])
+    assert (am[f == 0] >= 2).all() and (am[(f != 0) & (f != -7) & (f != -1)] <= am.max()).all()
+    assert (f == 0).mean() > 0.05
+    sub = [0, 13, 63]
+    bs = {k: (np.ascontiguousarray(val[sub]) if k != "params" else val) for k, val in b.items()}
+    orc = _oracle(bs)
+    for g, o in zip((d[sub], v[sub], f[sub], am[sub]), orc[:4]):
+        assert np.array_equal(g, o, equal_nan=True)
+
+
 def test_newtsukuba_golden_pair():
     """The reference's own fixture (tests/vo/semi_dense/test_semi_dense.py:40-73) with the values
     the oracle pinned in tests/golden/."""
