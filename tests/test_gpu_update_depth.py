@@ -140,6 +140,41 @@ def test_dense_texture_most_pixels_reach_the_search():
     assert_parity(gpu, orc)
 
 
+def test_general_poses_distinct_cameras_and_tiny_images():
+    """Key pose != identity, every reference with its own intrinsics, images smaller than a tile."""
+    rng = np.random.default_rng(77)
+    it = scene.make_keyframe(78, R=3, H=90, W=130, cam=np.array([115., 112., 64.2, 44.7]))
+    # move the whole rig by a rigid transform G: geometry is unchanged, the numbers are not
+    G = scene.pose(scene.rotation(0.3, -0.7, 1.1), (12.0, -40.0, 7.5))
+    it["T_wk"] = G @ it["T_wk"]
+    it["T_wr"] = np.stack([G @ T for T in it["T_wr"]])
+    it["ref_cams"] = it["ref_cams"] * rng.uniform(0.97, 1.03, it["ref_cams"].shape)
+    b = scene.stack_keyframes([it])
+    orc = _oracle(b)
+    assert (orc[2] == 0).sum() > 100
+    assert_parity(_gpu(b), orc)
+    for H, W in [(1, 1), (3, 5), (5, 70), (9, 9)]:
+        small = scene.make_keyframe(80 + H, R=2, H=H, W=W, cam=np.array([20., 20., (W - 1) / 2., (H - 1) / 2.]))
+        small["key_img"] = rng.random((H, W))
+        small["ref_imgs"] = rng.random((2, H, W))
+        small["age"] = rng.integers(0, 3, (H, W)).astype(np.uint64)
+        bs = scene.stack_keyframes([small, small])
+        assert_parity(_gpu(bs), _oracle(bs))
+
+
+def test_many_small_keyframes_in_one_launch():
+    """P = 300 keyframes (grid.z), one reference each."""
+    it = scene.make_pair(90, H=24, W=64, cam=np.array([50., 50., 31.5, 11.5]))
+    rng = np.random.default_rng(91)
+    items = []
+    for k in range(300):
+        c = dict(it)
+        c["prior_variance"] = 10.0 ** rng.uniform(-3.0, 0.0, size=(24, 64))
+        items.append(c)
+    b = scene.stack_keyframes(items)
+    assert_parity(_gpu(b, hist=True), _oracle(b))
+
+
 def test_every_flag_is_reachable_and_matches():
     """Hand-made priors that drive pixels into each failure branch (hypothesis.rs:21-37,
     semi_dense.rs:27-40,62-81): negative prior, out-of-range hypothesis, behind the reference."""
