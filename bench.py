@@ -233,6 +233,14 @@ def run_b200(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # one process per GPU: run on (and allocate pinned memory from) the NUMA node next to it
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        except Exception:
+            pass
+    if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     if args.plan >= 0:
         _lib.check(_lib.set_kernel_plan(args.plan))
