@@ -105,17 +105,21 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
-def time_cpu(ora, b, n_keyframes, threads, budget_s=20.0, max_reps=5):
+def time_cpu(ora, b, n_keyframes, threads, budget_s=20.0, max_reps=5, keep=None):
+    """Best of up to max_reps runs of the oracle pipeline on the first n_keyframes keyframes.
+    keep (a list) receives the (depth, variance, flag) maps of the last run."""
     sl = slice(0, n_keyframes)
     cpu_pipeline(ora, b, slice(0, min(n_keyframes, threads)), threads)      # warm-up
-    best, spent, reps = None, 0.0, 0
+    best, spent, reps, res = None, 0.0, 0, None
     while reps < max_reps and (reps < 2 or spent < budget_s):
         t0 = time.perf_counter()
-        cpu_pipeline(ora, b, sl, threads)
+        res = cpu_pipeline(ora, b, sl, threads)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
         spent += dt
         reps += 1
+    if keep is not None:
+        keep.extend(res)
     return n_keyframes * H * W / best, best, reps
 
 
@@ -416,10 +420,15 @@ def run_b200(args, rank, world, local_rank):
         import oracle as ora
         threads = host_threads()
         n_kf = min(B, max(threads, 8))
-        v, best, reps = time_cpu(ora, b, n_kf, threads)
+        cpu_maps = []
+        v, best, reps = time_cpu(ora, b, n_kf, threads, keep=cpu_maps)
         v1, _, _ = time_cpu(ora, b, 2, 1, budget_s=3.0, max_reps=3)
+        # the CPU run and the GPU run did the same work: identical maps on the sampled keyframes
+        same_maps = all(np.array_equal(c, g[:n_kf].cpu().numpy(), equal_nan=True)
+                        for c, g in zip(cpu_maps, out))
         line["cpu_baseline"] = {
             "value": v, "unit": UNIT, "cores": threads, "kind": "port", "single_thread_value": v1,
+            "maps_identical_to_gpu": bool(same_maps),
             "sample": f"{n_kf} of the step's {B} keyframes, best of {reps} runs, "
                       f"{1e3 * best / n_kf:.2f} ms/keyframe, OpenMP over keyframes"}
     print(json.dumps(line), flush=True)
