@@ -82,13 +82,19 @@ const char *tdk_version(void);
  *       (id, var) = fusion(inv(prior_depth), inv(new_depth), prior_variance, new_variance);
  *       depth = inv(id) -- identical to calling tdk_fusion_dev(depth_domain=1) afterwards,
  *       without the second pass over HBM
- *   workspace: tdk_update_depth_workspace_bytes(P,R,H,W) bytes of device scratch (status words,
- *       per-pair constants, and one u32 queue slot per pixel for the pixels that reach the search)
+ *   workspace: device scratch -- status words, per-pair constants, one u32 queue slot per pixel
+ *       for the pixels that reach the search, and, for up to 64 keyframes at a time, 137 bytes per
+ *       pixel for the search lines (128-byte record, length class, sort position; worst case =
+ *       every pixel is searched).  tdk_update_depth_workspace_bytes(P,R,H,W) is the size that runs
+ *       fastest (min(P,64) keyframes per sub-batch; 2.7 GB for 64 VGA keyframes);
+ *       tdk_update_depth_workspace_bytes_min(P,R,H,W) is the least that is accepted (one keyframe
+ *       per sub-batch); anything in between is used as far as it goes
  *
  * tdk_update_depth_status() copies the launch's status word back (synchronises the stream) and
  * returns TDK_OK / TDK_ERR_AGE / TDK_ERR_SINGULAR / TDK_ERR_SEARCH_LEN.
  */
 size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R, int64_t H, int64_t W);
+size_t tdk_update_depth_workspace_bytes_min(int64_t P, int64_t R, int64_t H, int64_t W);
 
 int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const double *T_wk,
                          const double *ref_imgs, const double *ref_cams, const double *T_wr,
@@ -143,9 +149,12 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 void *stream);
 
 /* Tuning knob with no counterpart in the reference: how update_depth is mapped onto kernels.
- * 0 (default) = two kernels: a sieve over all pixels that queues the survivors of the gradient test
- * in the workspace, then a search kernel over 256 queued pixels per CTA; 1 = one kernel, each CTA
- * compacts and searches its own 64x4 tile.  Results do not depend on it. */
+ * 2 (default) = a sieve over all pixels that queues the survivors of the gradient test in the
+ * workspace, a kernel that sets up their search lines, a counting sort of the lines by length, and a
+ * search kernel in which every warp walks 32 lines of equal length; 0 = the sieve, then one search
+ * kernel over 256 queued pixels per CTA (smaller workspace: 4 bytes per pixel); 1 = one kernel, each
+ * CTA compacts and searches its own 64x4 tile (what tdk_update_depth_static_dev runs).
+ * Results do not depend on it. */
 int tdk_set_kernel_plan(int plan);
 
 /* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,

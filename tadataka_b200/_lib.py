@@ -36,7 +36,9 @@ def _sig(name, restype, *argtypes):
 last_error = _sig("tdk_last_error", C.c_char_p)
 version = _sig("tdk_version", C.c_char_p)
 set_kernel_plan = _sig("tdk_set_kernel_plan", C.c_int, C.c_int)
+DEFAULT_PLAN = 2   # sieve + length-sorted line records (update_depth.cu)
 update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64, I64, I64)
+update_depth_workspace_bytes_min = _sig("tdk_update_depth_workspace_bytes_min", SZ, I64, I64, I64, I64)
 update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
                         I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_frames_dev = _sig("tdk_update_depth_frames_dev", C.c_int, P, P, P, P, P, P, P, P, P,
@@ -74,6 +76,7 @@ dvo_photometric_error_dev = _sig("tdk_dvo_photometric_error_dev", C.c_int, P, P,
 # every symbol include/tdk.h declares (tests check the header against this list and the .so)
 EXPORTS = [
     "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
+    "tdk_update_depth_workspace_bytes_min",
     "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_status",
     "tdk_update_depth_static_dev",
     "tdk_update_depth_host", "tdk_estimate_debug_host", "tdk_fusion_dev", "tdk_regularize_dev",

@@ -45,8 +45,18 @@ struct UpdArgs {
     int *dbg;
     unsigned long long *hist;
     int *status;
-    unsigned int *cand;         // two-kernel plan: [P, H*W] candidate pixel indices
-    unsigned int *cand_count;   // two-kernel plan: [P] queue lengths
+    unsigned int *cand;         // queue plans: [P, H*W] candidate pixel indices
+    unsigned int *cand_count;   // queue plans: [P] queue lengths
+    // sorted plan, all indexed by the keyframe's position in the current sub-batch (blockIdx.z):
+    double2 *rec;               // [S, H*W] 128 bytes per queue slot: phase A1 results written by the sieve
+                                //           (field-major inside each chunk of 256 slots), replaced by
+                                //           the line records (one 128-byte record per slot) in lines_kernel
+    unsigned char *len_class;   // [S, H*W] min(line length, 63) per queue slot, 0 = dropped in A2
+    unsigned int *order;        // [S, H*W] queue slots of the live lines, longest class first
+    unsigned int *len_hist;     // [S, 64] lines per length class
+    unsigned int *len_cursor;   // [S, 64] slots handed out per class while `order` is filled
+    size_t rec_stride;          // slots per keyframe in rec: H*W rounded up to whole chunks of 256
+    int p0;                     // first keyframe of the sub-batch (blockIdx.z + p0 indexes maps, keys, pairs, cand)
     double vmin, vmax, geo, photo, step, min_grad;
     int P, R, H, W, tiles_x, tiles_y, fuse;
 };
@@ -126,9 +136,12 @@ __global__ void pair_setup_kernel(const double *key_imgs, const double *const *k
                                   const double *ref_imgs, const double *const *ref_ptrs,
                                   const double *__restrict__ ref_cams, const double *__restrict__ T_wr,
                                   int P, int R, size_t hw, TdkKeyConst *keys, TdkPairConst *pairs,
-                                  int *status)
+                                  int *status, unsigned int *zero_words, int n_zero_words)
 {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    // the queue plans' counters (queue lengths, line-length histograms) start at zero; clearing them
+    // here saves two memset nodes per launch
+    for (int i = idx; i < n_zero_words; i += gridDim.x * blockDim.x) zero_words[i] = 0u;
     if (idx >= P * R) return;
     const int p = idx / R, r = idx % R;
     if (r == 0) {
@@ -282,62 +295,89 @@ __device__ __forceinline__ void queue_push(CtaQueue &Q, int slot, const A1Result
     Q.owner[slot] = (unsigned short)owner;
 }
 
+// What phases B and C need of a candidate that passed A2.  Lives in registers, in the shared-memory
+// queue (one-kernel plan) or in a 128-byte record of the workspace (sorted plan).
+struct LineRec {
+    double k0, k1, k2, k3, k4;      // normalised key window, in the direction the reference sampled it
+    double xminx, xminy, ux, uy;    // near end and unit direction of the reference line
+    double rdx, rdy;                // x_max_ref - x_min_ref
+    double g, kstep;                // key gradient norm, key step
+    int n;                          // samples on the reference line
+};
+
+// Phase A2 in registers.  Returns 1 (survivor, o filled) or a final flag (o.n = 0).
+__device__ __forceinline__ int phase_a2_core(const UpdArgs &a, const TdkPairConst *__restrict__ pc, double xk,
+                                             double yk, double v, const A1Result &c, double wm1, double hm1,
+                                             LineRec &o)
+{
+    const double *__restrict__ T = pc->T;
+    const double idp = c.idp;
+    o.n = 0;
+    // hypothesis.rs:54-61, depth.rs:25-30
+    const double lo = tdk::clampd(idp - TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
+    const double hi = tdk::clampd(idp + TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
+    const double dmin = tdk::inv(hi), dmax = tdk::inv(lo);
+    // calc_ref_ends, semi_dense.rs:51-60
+    double xminx, xminy, xmaxx, xmaxy, zz;
+    tdk::warp_point(T, xk, yk, dmin, xminx, xminy, zz);
+    tdk::warp_point(T, xk, yk, dmax, xmaxx, xmaxy, zz);
+    const double rdx = xmaxx - xminx, rdy = xmaxy - xminy;
+    // calc_key_direction, semi_dense.rs:42-49: d if ref_dir . d > 0 else -d
+    const double kdx = xk - pc->ex, kdy = yk - pc->ey;
+    const bool keep = rdx * kdx + rdy * kdy > 0.;
+    double k0 = c.ki[0], k1 = c.ki[1], k2 = c.ki[2], k3 = c.ki[3], k4 = c.ki[4];
+    double g = c.gf;
+    if (!keep) {   // the reference sampled along -d: same five values in reverse order
+        double tmp = k0; k0 = k4; k4 = tmp;
+        tmp = k1; k1 = k3; k3 = tmp;
+        g = c.gr;
+    }
+    if (g < a.min_grad) return TDK_FLAG_INSUFFICIENT_GRADIENT;
+    // ref_coordinates + check_us_ref, epipolar.rs:38-54, semi_dense.rs:62-81
+    const double L = sqrt(rdx * rdx + rdy * rdy);
+    const double ux = rdx / (L + TDK_EPS), uy = rdy / (L + TDK_EPS);
+    const double nf = L / a.step;
+    int n = 0;
+    if (nf > 0.) n = nf >= 2147483647. ? 2147483647 : (int)nf;   // Rust `as usize`
+    if (n < 5) return TDK_FLAG_REF_EPIPOLAR_TOO_SHORT;
+    const double fx0 = (xminx + (0. * a.step) * ux) * pc->rfx + pc->rox;
+    const double fy0 = (xminy + (0. * a.step) * uy) * pc->rfy + pc->roy;
+    if (!tdk::in_range(fx0, fy0, wm1, hm1)) return TDK_FLAG_REF_CLOSE_OUT_OF_RANGE;
+    const double sl = (double)(n - 1) * a.step;
+    const double fx1 = (xminx + sl * ux) * pc->rfx + pc->rox;
+    const double fy1 = (xminy + sl * uy) * pc->rfy + pc->roy;
+    if (!tdk::in_range(fx1, fy1, wm1, hm1)) return TDK_FLAG_REF_FAR_OUT_OF_RANGE;
+    if (n > TDK_MAX_SEARCH_SAMPLES) {
+        atomicExch(&a.status[TDK_ST_SEARCH_LEN], 1);
+        n = TDK_MAX_SEARCH_SAMPLES;
+    }
+    // normalise the key window once (intensities.rs:20 does it for every window)
+    const double kn = sqrt(k0 * k0 + k1 * k1 + k2 * k2 + k3 * k3 + k4 * k4);
+    if (kn != 0.) { k0 = k0 / kn; k1 = k1 / kn; k2 = k2 / kn; k3 = k3 / kn; k4 = k4 / kn; }
+    o.k0 = k0; o.k1 = k1; o.k2 = k2; o.k3 = k3; o.k4 = k4;
+    o.xminx = xminx; o.xminy = xminy; o.ux = ux; o.uy = uy; o.rdx = rdx; o.rdy = rdy;
+    o.g = g; o.kstep = c.kstep; o.n = n;
+    return 1;
+}
+
 // Phase A2 for queue slot q.  Returns 1 (survivor; Q.n[q] = line length) or a final flag (Q.n[q] = 0).
 __device__ __forceinline__ int phase_a2(const UpdArgs &a, CtaQueue &Q, int p, int q, double wm1, double hm1)
 {
     const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
-    const double *__restrict__ T = pc->T;
-    const double xk = Q.xk[q], yk = Q.yk[q];
-    const double idp = Q.idp[q], v = Q.v[q];
-    int f = 1, n = 0;
-    do {
-        // hypothesis.rs:54-61, depth.rs:25-30
-        const double lo = tdk::clampd(idp - TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
-        const double hi = tdk::clampd(idp + TDK_VARIANCE_FACTOR * v, a.vmin, a.vmax);
-        const double dmin = tdk::inv(hi), dmax = tdk::inv(lo);
-        // calc_ref_ends, semi_dense.rs:51-60
-        double xminx, xminy, xmaxx, xmaxy, zz;
-        tdk::warp_point(T, xk, yk, dmin, xminx, xminy, zz);
-        tdk::warp_point(T, xk, yk, dmax, xmaxx, xmaxy, zz);
-        const double rdx = xmaxx - xminx, rdy = xmaxy - xminy;
-        // calc_key_direction, semi_dense.rs:42-49: d if ref_dir . d > 0 else -d
-        const double kdx = xk - pc->ex, kdy = yk - pc->ey;
-        const bool keep = rdx * kdx + rdy * kdy > 0.;
-        double k0 = Q.k[0][q], k1 = Q.k[1][q], k2 = Q.k[2][q], k3 = Q.k[3][q], k4 = Q.k[4][q];
-        double g = Q.g[q];
-        if (!keep) {   // the reference sampled along -d: same five values in reverse order
-            double tmp = k0; k0 = k4; k4 = tmp;
-            tmp = k1; k1 = k3; k3 = tmp;
-            g = Q.grev[q];
-        }
-        if (g < a.min_grad) { f = TDK_FLAG_INSUFFICIENT_GRADIENT; break; }
-        // ref_coordinates + check_us_ref, epipolar.rs:38-54, semi_dense.rs:62-81
-        const double L = sqrt(rdx * rdx + rdy * rdy);
-        const double ux = rdx / (L + TDK_EPS), uy = rdy / (L + TDK_EPS);
-        const double nf = L / a.step;
-        if (nf > 0.) n = nf >= 2147483647. ? 2147483647 : (int)nf;   // Rust `as usize`
-        if (n < 5) { f = TDK_FLAG_REF_EPIPOLAR_TOO_SHORT; break; }
-        const double fx0 = (xminx + (0. * a.step) * ux) * pc->rfx + pc->rox;
-        const double fy0 = (xminy + (0. * a.step) * uy) * pc->rfy + pc->roy;
-        if (!tdk::in_range(fx0, fy0, wm1, hm1)) { f = TDK_FLAG_REF_CLOSE_OUT_OF_RANGE; break; }
-        const double sl = (double)(n - 1) * a.step;
-        const double fx1 = (xminx + sl * ux) * pc->rfx + pc->rox;
-        const double fy1 = (xminy + sl * uy) * pc->rfy + pc->roy;
-        if (!tdk::in_range(fx1, fy1, wm1, hm1)) { f = TDK_FLAG_REF_FAR_OUT_OF_RANGE; break; }
-        if (n > TDK_MAX_SEARCH_SAMPLES) {
-            atomicExch(&a.status[TDK_ST_SEARCH_LEN], 1);
-            n = TDK_MAX_SEARCH_SAMPLES;
-        }
-        // normalise the key window once (intensities.rs:20 does it for every window)
-        const double kn = sqrt(k0 * k0 + k1 * k1 + k2 * k2 + k3 * k3 + k4 * k4);
-        if (kn != 0.) { k0 = k0 / kn; k1 = k1 / kn; k2 = k2 / kn; k3 = k3 / kn; k4 = k4 / kn; }
-        Q.k[0][q] = k0; Q.k[1][q] = k1; Q.k[2][q] = k2; Q.k[3][q] = k3; Q.k[4][q] = k4;
-        Q.g[q] = g;
-        Q.xminx[q] = xminx; Q.xminy[q] = xminy;
-        Q.ux[q] = ux; Q.uy[q] = uy;
-        Q.rdx[q] = rdx; Q.rdy[q] = rdy;
-    } while (false);
-    Q.n[q] = f == 1 ? n : 0;
+    A1Result c;
+#pragma unroll
+    for (int k = 0; k < 5; k++) c.ki[k] = Q.k[k][q];
+    c.kstep = Q.kstep[q]; c.gf = Q.g[q]; c.gr = Q.grev[q]; c.idp = Q.idp[q]; c.r = Q.ref[q];
+    LineRec o;
+    const int f = phase_a2_core(a, pc, Q.xk[q], Q.yk[q], Q.v[q], c, wm1, hm1, o);
+    if (f == 1) {
+        Q.k[0][q] = o.k0; Q.k[1][q] = o.k1; Q.k[2][q] = o.k2; Q.k[3][q] = o.k3; Q.k[4][q] = o.k4;
+        Q.g[q] = o.g;
+        Q.xminx[q] = o.xminx; Q.xminy[q] = o.xminy;
+        Q.ux[q] = o.ux; Q.uy[q] = o.uy;
+        Q.rdx[q] = o.rdx; Q.rdy[q] = o.rdy;
+    }
+    Q.n[q] = o.n;
     return f;
 }
 
@@ -371,20 +411,19 @@ __device__ __forceinline__ double window_error(double s0, double s1, double s2, 
     return d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
 }
 
-// Phase C for a live queue slot q.  Returns the final flag; on SUCCESS nd / nv hold the new (or
-// fused) depth and variance.
-__device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, const TdkKeyConst &key, int p, int q,
-                                       size_t map_base, double &nd, double &nv)
+// Phase C in registers for the pixel (sx, sy) whose search returned `arg` (= argmin + 2).  Returns the
+// final flag; on SUCCESS nd / nv hold the new (or fused) depth and variance.  pv = prior variance.
+__device__ __forceinline__ int phase_c_core(const UpdArgs &a, const TdkKeyConst &key,
+                                            const TdkPairConst *__restrict__ pc, int arg, int sx, int sy, double xk,
+                                            double yk, double xminx, double xminy, double ux, double uy,
+                                            double rdx, double rdy, double g, double kstep, double pv,
+                                            size_t map_base, double &nd, double &nv)
 {
     const int W = a.W, H = a.H;
-    const int arg = Q.arg[q];
-    const int sx = Q.px[q] & 0xffff, sy = Q.px[q] >> 16;
-    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
     const double *__restrict__ T = pc->T;
-    const double xk = Q.xk[q], yk = Q.yk[q];
     const double s = (double)arg * a.step;
-    const double xr = Q.xminx[q] + s * Q.ux[q];
-    const double yr = Q.xminy[q] + s * Q.uy[q];
+    const double xr = xminx + s * ux;
+    const double yr = xminy + s * uy;
 
     // calc_depth0, triangulation.rs:8-36
     const double rzy = T[8] * xk + T[9] * yk + T[10] * 1.;
@@ -396,7 +435,6 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
     const double depth = (ti - tzz * x1i) / ((rzy * x1i - riy) + TDK_EPS);
 
     // calc_alpha, variance.rs:55-106
-    const double rdx = Q.rdx[q], rdy = Q.rdy[q];
     const double rn = sqrt(rdx * rdx + rdy * rdy);
     const double dhx = rn == 0. ? rdx : rdx / rn, dhy = rn == 0. ? rdy : rdy / rn;
     double xrefx, xrefy, zz;
@@ -429,7 +467,7 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
     if (gn != 0.) { gx = gx / gn; gy = gy / gn; }
     const double pp = lx2 * gx + ly2 * gy;
     const double geo_var = pp == 0. ? 1. / TDK_EPS : 1. / (pp * pp);
-    const double photo_var = 2. / (Q.g[q] / Q.kstep[q]);
+    const double photo_var = 2. / (g / kstep);
     const double variance = (alpha * alpha) * ((a.geo * a.geo) * geo_var + (a.photo * a.photo) * photo_var);
 
     const double idn = tdk::inv(depth);
@@ -438,7 +476,7 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
         nd = tdk::inv(idn);
         nv = variance;
         if (a.fuse) {   // fusion.rs:3-11 in inverse depth, as propagation.rs:27-34
-            const double pd = a.prior_d[map_base + (size_t)sy * W + sx], pv = Q.v[q];
+            const double pd = a.prior_d[map_base + (size_t)sy * W + sx];
             const double ia = tdk::inv(pd), ib = tdk::inv(nd);
             const double vs = pv + nv;
             nd = tdk::inv((ia * nv + ib * pv) / vs);
@@ -446,6 +484,16 @@ __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, cons
         }
     }
     return f;
+}
+
+// Phase C for a live queue slot q.
+__device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, const TdkKeyConst &key, int p, int q,
+                                       size_t map_base, double &nd, double &nv)
+{
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
+    return phase_c_core(a, key, pc, Q.arg[q], Q.px[q] & 0xffff, Q.px[q] >> 16, Q.xk[q], Q.yk[q], Q.xminx[q],
+                        Q.xminy[q], Q.ux[q], Q.uy[q], Q.rdx[q], Q.rdy[q], Q.g[q], Q.kstep[q], Q.v[q], map_base,
+                        nd, nv);
 }
 
 // Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
@@ -566,7 +614,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int p = blockIdx.z;
+    const int p = (int)blockIdx.z + a.p0;
     const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t map_base = (size_t)p * H * W;
@@ -646,13 +694,15 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
 // that is finished (and the provisional prior for candidates) and appends the candidates of its
 // tile to the keyframe's queue in global memory.  search_kernel then takes 256 candidates of one
 // keyframe per CTA, so phases A2 / B / C run with every thread busy.
+__device__ __forceinline__ void a1_store(double2 *rec_base, size_t slot, const A1Result &c, double v, int px);   // below, with the sorted plan
+
 __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kernel(const UpdArgs a)
 {
     __shared__ double s_xk[TILE_W], s_yk[TILE_H];
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int p = blockIdx.z;
+    const int p = (int)blockIdx.z + a.p0;
     const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
@@ -674,13 +724,13 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     __syncthreads();
 
     int flag = TDK_FLAG_NOT_PROCESSED;
+    A1Result c;
     if (valid) {
         double out_d = d;
         if (age != 0) {
             if (age > (uint64_t)a.R) {
                 atomicExch(&a.status[TDK_ST_AGE], 1);
             } else {
-                A1Result c;
                 flag = phase_a1(a, key, p, s_xk[lx], s_yk[ly], age, d, v, wm1, hm1, out_d, c);
             }
         }
@@ -698,7 +748,12 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
         unsigned int base = 0;
         if (lane == 0) base = atomicAdd(a.cand_count + p, (unsigned int)__popc(cmask));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (flag == 1) a.cand[map_base + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
+        if (flag == 1) {
+            const unsigned int slot = base + __popc(cmask & ((1u << lane) - 1u));
+            a.cand[map_base + slot] = (unsigned int)(y * W + x);
+            // sorted plan: hand the A1 results to lines_kernel through the slot's place in `rec`
+            if (a.rec) a1_store(a.rec, (size_t)blockIdx.z * a.rec_stride + slot, c, v, x | (y << 16));
+        }
     }
     if (a.hist) {
         __syncthreads();
@@ -713,7 +768,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int p = blockIdx.z;
+    const int p = (int)blockIdx.z + a.p0;
     const int total = (int)a.cand_count[p];
     const int W = a.W, H = a.H;
     const size_t map_base = (size_t)p * H * W;
@@ -765,14 +820,272 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
 }
 
 // ---------------------------------------------------------------------------------------------
+// Sorted plan (default).  The sieve also leaves the phase A1 results of every queued pixel in the
+// workspace; then three kernels per sub-batch of keyframes:
+//   lines_kernel  thread per queued pixel: phase A2, a 128-byte line record into the workspace (in
+//                 place of the A1 results), the line's length class and a per-keyframe histogram;
+//   order_kernel  counting sort by length class: fills `order` with the live queue slots, longest first;
+//   match_kernel  a warp takes 32 consecutive entries of `order` -- lines of (nearly) equal length --
+//                 and every lane walks its own line exactly as intensities.rs:16-29 does, then runs
+//                 phase C and stores.  No shared-memory queue and no CTA barrier: a warp never waits
+//                 for another warp's longer lines.  Lines of LEN_CLASSES-1 samples or more take a whole
+//                 warp each (search_line_warp).
+constexpr int LEN_CLASSES = 64;
+#ifndef TDK_LINES_MIN_CTAS
+#define TDK_LINES_MIN_CTAS 4
+#endif
+#ifndef TDK_MATCH_MIN_CTAS
+#define TDK_MATCH_MIN_CTAS 4
+#endif
+constexpr int LINES_MIN_CTAS = TDK_LINES_MIN_CTAS, MATCH_MIN_CTAS = TDK_MATCH_MIN_CTAS;
+#ifndef TDK_MATCH_STAGE
+#define TDK_MATCH_STAGE 0
+#endif
+constexpr int MATCH_STAGE = TDK_MATCH_STAGE;   // line samples staged per thread in shared memory (0 = none)
+constexpr size_t MATCH_SMEM_BYTES = (size_t)MATCH_STAGE * BLOCK * sizeof(double);
+constexpr int REC_DOUBLE2 = 8;   // 128 bytes per queue slot
+constexpr int REC_DOUBLES = 2 * REC_DOUBLE2;
+constexpr int A1_FIELDS = 11;    // ki[5], kstep, gf, gr, idp, prior variance, {ref | pixel}
+static_assert(A1_FIELDS <= REC_DOUBLES, "the A1 results must fit the slot they share with the line record");
+
+struct RecTail { int n, ref, px, pad; };
+
+// The sieve's hand-over: field f of queue slot s goes to word f * BLOCK + (s % BLOCK) of the chunk of
+// BLOCK slots that s belongs to, so both the sieve's warps (consecutive slots) and lines_kernel
+// (thread t <-> slot first + t) touch consecutive words.
+__device__ __forceinline__ void a1_store(double2 *rec_base, size_t slot, const A1Result &c, double v, int px)
+{
+    double *chunk = reinterpret_cast<double *>(rec_base) + (slot & ~(size_t)(BLOCK - 1)) * REC_DOUBLES;
+    const int j = (int)(slot & (BLOCK - 1));
+#pragma unroll
+    for (int k = 0; k < 5; k++) chunk[k * BLOCK + j] = c.ki[k];
+    chunk[5 * BLOCK + j] = c.kstep;
+    chunk[6 * BLOCK + j] = c.gf;
+    chunk[7 * BLOCK + j] = c.gr;
+    chunk[8 * BLOCK + j] = c.idp;
+    chunk[9 * BLOCK + j] = v;
+    reinterpret_cast<int2 *>(chunk)[10 * BLOCK + j] = make_int2(c.r, px);
+}
+
+__device__ __forceinline__ void record_store(double2 *__restrict__ r, const LineRec &l, int ref, int px, double v)
+{
+    r[0] = make_double2(l.k0, l.k1);
+    r[1] = make_double2(l.k2, l.k3);
+    r[2] = make_double2(l.k4, l.xminx);
+    r[3] = make_double2(l.xminy, l.ux);
+    r[4] = make_double2(l.uy, l.rdx);
+    r[5] = make_double2(l.rdy, l.g);
+    r[6] = make_double2(l.kstep, v);
+    RecTail t{l.n, ref, px, 0};
+    r[7] = *reinterpret_cast<const double2 *>(&t);
+}
+
+__global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kernel(const UpdArgs a)
+{
+    __shared__ unsigned int s_hist[10], s_len[LEN_CLASSES];
+    const int tid = threadIdx.x;
+    const int pl = blockIdx.z, p = pl + a.p0;
+    const int total = (int)a.cand_count[p];
+    if ((int)blockIdx.x * BLOCK >= total) return;
+    const int W = a.W, H = a.H;
+    const size_t hw = (size_t)H * W, map_base = (size_t)p * hw, ws_base = (size_t)pl * hw;
+    const TdkKeyConst key = a.keys[p];
+    const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
+    const size_t rec_base = (size_t)pl * a.rec_stride;
+    if (tid < 10) s_hist[tid] = 0;
+    if (tid < LEN_CLASSES) s_len[tid] = 0;
+
+    for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
+        const int i = first + tid;
+        const bool live = i < total;
+        A1Result c;
+        double v = 0.;
+        int px = 0;
+        if (live) {
+            const double *__restrict__ chunk = reinterpret_cast<const double *>(a.rec) + (rec_base + first) * REC_DOUBLES;
+#pragma unroll
+            for (int k = 0; k < 5; k++) c.ki[k] = chunk[k * BLOCK + tid];
+            c.kstep = chunk[5 * BLOCK + tid];
+            c.gf = chunk[6 * BLOCK + tid];
+            c.gr = chunk[7 * BLOCK + tid];
+            c.idp = chunk[8 * BLOCK + tid];
+            v = chunk[9 * BLOCK + tid];
+            const int2 t = reinterpret_cast<const int2 *>(chunk)[10 * BLOCK + tid];
+            c.r = t.x;
+            px = t.y;
+        }
+        __syncthreads();   // every A1 result of this chunk is in registers: the records may overwrite them
+        if (!live) continue;
+        const int x = px & 0xffff, y = px >> 16;
+        const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
+        const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + c.r;
+        LineRec l;
+        const int flag = phase_a2_core(a, pc, xk, yk, v, c, wm1, hm1, l);
+        int cls = 0;
+        if (flag == 1) {
+            cls = min(l.n, LEN_CLASSES - 1);
+            record_store(a.rec + (rec_base + i) * REC_DOUBLE2, l, c.r, px, v);
+            atomicAdd(&s_len[cls], 1u);
+        } else {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
+            a.out_f[map_base + (size_t)y * W + x] = (long long)flag;
+            if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+        }
+        a.len_class[ws_base + i] = (unsigned char)cls;
+    }
+    __syncthreads();
+    if (tid < LEN_CLASSES && s_len[tid]) atomicAdd(&a.len_hist[pl * LEN_CLASSES + tid], s_len[tid]);
+    if (a.hist && tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+}
+
+// first position in `order` of each length class, longest class first: start[c] = sum of hist[c' > c]
+__device__ __forceinline__ void class_starts(const unsigned int *__restrict__ hist, unsigned int *s_start, int tid)
+{
+    if (tid < 32) {
+        const unsigned int c_hi = hist[LEN_CLASSES - 1 - 2 * tid], c_lo = hist[LEN_CLASSES - 2 - 2 * tid];
+        unsigned int incl = c_hi + c_lo;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (tid >= off) incl += o;
+        }
+        s_start[LEN_CLASSES - 1 - 2 * tid] = incl - c_hi - c_lo;
+        s_start[LEN_CLASSES - 2 - 2 * tid] = incl - c_lo;
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs a)
+{
+    __shared__ unsigned int s_start[LEN_CLASSES], s_cnt[LEN_CLASSES], s_off[LEN_CLASSES];
+    const int tid = threadIdx.x;
+    const int pl = blockIdx.z, p = pl + a.p0;
+    const int total = (int)a.cand_count[p];
+    if ((int)blockIdx.x * BLOCK >= total) return;
+    const size_t ws_base = (size_t)pl * a.H * a.W;
+    class_starts(a.len_hist + pl * LEN_CLASSES, s_start, tid);
+    for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
+        if (tid < LEN_CLASSES) s_cnt[tid] = 0;
+        __syncthreads();
+        const int i = first + tid;
+        const int cls = i < total ? (int)a.len_class[ws_base + i] : 0;
+        unsigned int rank = 0;
+        if (cls) rank = atomicAdd(&s_cnt[cls], 1u);
+        __syncthreads();
+        if (tid < LEN_CLASSES && tid > 0 && s_cnt[tid])
+            s_off[tid] = atomicAdd(&a.len_cursor[pl * LEN_CLASSES + tid], s_cnt[tid]);
+        __syncthreads();
+        if (cls) a.order[ws_base + s_start[cls] + s_off[cls] + rank] = (unsigned int)i;
+    }
+}
+
+__global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kernel(const UpdArgs a)
+{
+    __shared__ unsigned int s_hist[10], s_start[LEN_CLASSES];
+#if TDK_MATCH_STAGE > 0
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    double *s_stage = reinterpret_cast<double *>(s_dyn);   // [MATCH_STAGE][BLOCK]
+#endif
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int pl = blockIdx.z, p = pl + a.p0;
+    const int W = a.W, H = a.H;
+    const size_t hw = (size_t)H * W, map_base = (size_t)p * hw, ws_base = (size_t)pl * hw;
+    if (tid < 10) s_hist[tid] = 0;
+    class_starts(a.len_hist + pl * LEN_CLASSES, s_start, tid);
+    __syncthreads();
+    const int nlong = (int)s_start[LEN_CLASSES - 2];   // lines of class 63 come first
+    const int nlive = (int)s_start[0];                 // class 0 (dropped lines) would start here
+    const int nitems = nlong + (nlive - nlong + 31) / 32;
+    const TdkKeyConst key = a.keys[p];
+    const int warps = BLOCK / 32;
+
+    for (int item = (int)blockIdx.x * warps + (tid >> 5); item < nitems; item += (int)gridDim.x * warps) {
+        __syncwarp();   // `item` is warp-uniform: lanes that left the previous item early wait here
+        const bool whole_warp = item < nlong;
+        const int pos = whole_warp ? item : nlong + (item - nlong) * 32 + lane;
+        if (pos >= nlive) continue;
+        const unsigned int slot = a.order[ws_base + pos];
+        const double2 *__restrict__ r = a.rec + ((size_t)pl * a.rec_stride + slot) * REC_DOUBLE2;
+        const double2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4];
+        const double2 r7 = r[7];
+        const RecTail t = *reinterpret_cast<const RecTail *>(&r7);
+        const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + t.ref;
+        const LineGeom g{pc->ref, pc->rfx, pc->rfy, pc->rox, pc->roy, r2.y, r3.x, r3.y, r4.x};
+        const double k0 = r0.x, k1 = r0.y, k2 = r1.x, k3 = r1.y, k4 = r2.x;
+        int arg = 0;
+        if (whole_warp) {
+            arg = search_line_warp(g, t.n, a.step, W, H, k0, k1, k2, k3, k4, lane);
+            if (lane != 0) continue;
+        } else {
+            double s0 = line_sample(g, 0, a.step, W, H), s1 = line_sample(g, 1, a.step, W, H);
+            double s2 = line_sample(g, 2, a.step, W, H), s3 = line_sample(g, 3, a.step, W, H);
+            double best = INFINITY;
+#if TDK_MATCH_STAGE > 0
+            // Samples are fetched MATCH_STAGE at a time into a thread-private column of shared memory
+            // (independent loads, so many are in flight at once), then the windows are evaluated from
+            // there in the reference's order: first minimum kept by `e < best`.
+            double *__restrict__ mine = s_stage + tid;
+            for (int next = 4; next < t.n; next += MATCH_STAGE) {
+                const int cnt = min(MATCH_STAGE, t.n - next);
+#pragma unroll 4
+                for (int j = 0; j < cnt; j++) mine[j * BLOCK] = line_sample(g, next + j, a.step, W, H);
+                for (int j = 0; j < cnt; j++) {
+                    const double s4 = mine[j * BLOCK];
+                    const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+                    if (e < best) { best = e; arg = next + j - 4; }
+                    s0 = s1; s1 = s2; s2 = s3; s3 = s4;
+                }
+            }
+#else
+            for (int i = 0; i + 4 < t.n; i++) {
+                const double s4 = line_sample(g, i + 4, a.step, W, H);
+                const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
+                if (e < best) { best = e; arg = i; }
+                s0 = s1; s1 = s2; s2 = s3; s3 = s4;
+            }
+#endif
+        }
+        arg += 2;   // intensities.rs:32-36
+        // ---- phase C and the scattered store
+        const int sx = t.px & 0xffff, sy = t.px >> 16;
+        const double xk = ((double)sx - key.ox) / key.fx, yk = ((double)sy - key.oy) / key.fy;
+        const double2 r5 = r[5], r6 = r[6];
+        double nd, nv;
+        const int f = phase_c_core(a, key, pc, arg, sx, sy, xk, yk, r2.y, r3.x, r3.y, r4.x, r4.y, r5.x, r5.y,
+                                   r6.x, r6.y, map_base, nd, nv);
+        const size_t at = map_base + (size_t)sy * W + sx;
+        if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
+        else a.out_f[at] = (long long)f;
+        if (a.dbg) a.dbg[at] = arg;
+        if (a.hist) atomicAdd(&s_hist[-f], 1u);
+    }
+    if (a.hist) {
+        __syncthreads();
+        if (tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t status, keys, pairs, key_ptrs, ref_ptrs, total_tile, cand_count, cand, total;
+    size_t status, keys, pairs, key_ptrs, ref_ptrs, total_tile, cand_count, cand, total_queue;
+    size_t len_hist, counters_end, len_class, order, rec, total;
+    int64_t sub;   // keyframes per sub-batch of the sorted plan
 };
 
-// total_tile: what the one-kernel plan needs; total: plus the candidate queues of the two-kernel plan
-WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W)
+// The sorted plan's per-candidate arrays (137 bytes per pixel of a keyframe: worst case, every pixel
+// queued) are sized for a sub-batch of keyframes and reused by the sub-batches of a larger launch;
+// the kernels of successive sub-batches run in stream order.  Every sub-batch pays four kernel
+// tails, so bigger is faster (64 VGA keyframes: 24.8 / 22.3 / 20.8 / 20.0 us per keyframe with
+// sub-batches of 8 / 16 / 32 / 64).  tdk_update_depth_workspace_bytes() asks for min(P, SUB_BATCH)
+// keyframes' worth; launch() uses as many as the workspace it is given holds, down to one.
+#ifndef TDK_SUB_BATCH
+#define TDK_SUB_BATCH 64
+#endif
+constexpr int64_t SUB_BATCH = TDK_SUB_BATCH;
+
+// total_tile: what the one-kernel plan needs; total_queue: plus the candidate queues of the
+// two-kernel plan; total: plus the line records of the sorted plan
+WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W, int64_t sub = SUB_BATCH)
 {
     WsLayout l;
     size_t off = 0;
@@ -782,14 +1095,25 @@ WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W)
     l.key_ptrs = off; off = align_up(off + (size_t)P * sizeof(void *), 256);
     l.ref_ptrs = off; off = align_up(off + (size_t)P * R * sizeof(void *), 256);
     l.total_tile = off;
+    l.sub = P < sub ? P : sub;
+    const size_t S = (size_t)l.sub, hw = (size_t)H * W;
+    // counters, contiguous so that pair_setup_kernel clears them in one sweep (the two-kernel plan
+    // only uses cand_count; 512 bytes per sub-batch keyframe are not worth a second layout)
     l.cand_count = off; off = align_up(off + (size_t)P * sizeof(unsigned int), 256);
+    l.len_hist = off; off = align_up(off + S * 2 * LEN_CLASSES * sizeof(unsigned int), 256);   // hist, then cursor
+    l.counters_end = off;
     l.cand = off; off = align_up(off + (size_t)P * H * W * sizeof(unsigned int), 256);
+    l.total_queue = off;
+    l.len_class = off; off = align_up(off + S * hw, 256);
+    l.order = off; off = align_up(off + S * hw * sizeof(unsigned int), 256);
+    // records: whole chunks of BLOCK slots (the sieve addresses the A1 results by chunk)
+    l.rec = off; off = align_up(off + S * align_up(hw, BLOCK) * REC_DOUBLE2 * sizeof(double2), 256);
     l.total = off;
     return l;
 }
 
-enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1 };
-int g_plan = PLAN_TWO_KERNELS;
+enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
+int g_plan = PLAN_SORTED;
 
 
 int launch(const double *key_imgs, const double *const *key_ptrs_host, const double *key_cams,
@@ -815,8 +1139,10 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         tdk_set_error("tdk_update_depth: ref_step_size must be > 0 (got %g)", params[4]);
         return TDK_ERR_INVALID;
     }
-    const WsLayout l = ws_layout(P, R, H, W);
-    const size_t need = plan == PLAN_ONE_KERNEL ? l.total_tile : l.total;
+    WsLayout l = ws_layout(P, R, H, W);
+    if (plan == PLAN_SORTED)   // as many keyframes per sub-batch as the workspace holds
+        while (l.sub > 1 && workspace_bytes < l.total) l = ws_layout(P, R, H, W, l.sub - 1);
+    const size_t need = plan == PLAN_ONE_KERNEL ? l.total_tile : plan == PLAN_TWO_KERNELS ? l.total_queue : l.total;
     if (workspace_bytes < need) {
         tdk_set_error("tdk_update_depth: workspace %zu < required %zu", workspace_bytes, need);
         return TDK_ERR_WORKSPACE;
@@ -848,7 +1174,9 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     const int npairs = (int)(P * R);
     pair_setup_kernel<<<(npairs + 127) / 128, 128, 0, stream>>>(
         key_imgs, key_ptrs, key_cams, T_wk, ref_imgs, ref_ptrs, ref_cams, T_wr, (int)P, (int)R,
-        (size_t)H * W, keys, pairs, status);
+        (size_t)H * W, keys, pairs, status,
+        plan == PLAN_ONE_KERNEL ? nullptr : (unsigned int *)(ws + l.cand_count),
+        plan == PLAN_ONE_KERNEL ? 0 : (int)((l.counters_end - l.cand_count) / sizeof(unsigned int)));
     TDK_CUDA(cudaGetLastError());
 
     UpdArgs a;
@@ -859,6 +1187,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmin = 1. / (params[1] + TDK_EPS_INV);
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
+    a.p0 = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr; a.len_hist = nullptr; a.len_cursor = nullptr;
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
     static bool attr_set[64] = {};
     int dev = 0;
@@ -868,6 +1197,9 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                                       (int)CTA_SMEM_BYTES));
         TDK_CUDA(cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)CTA_SMEM_BYTES));
+        if (MATCH_SMEM_BYTES > 0)
+            TDK_CUDA(cudaFuncSetAttribute(update_depth_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)MATCH_SMEM_BYTES));
         attr_set[dev] = true;
     }
     if (plan == PLAN_ONE_KERNEL) {
@@ -876,11 +1208,31 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     } else {
         a.cand_count = (unsigned int *)(ws + l.cand_count);
         a.cand = (unsigned int *)(ws + l.cand);
-        TDK_CUDA(cudaMemsetAsync(a.cand_count, 0, (size_t)P * sizeof(unsigned int), stream));
-        update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
-        TDK_CUDA(cudaGetLastError());
-        const dim3 sgrid((unsigned)((tiles_x * tiles_y + 3) / 4), 1u, (unsigned)P);
-        update_depth_search_kernel<<<sgrid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+        const unsigned qx = (unsigned)((tiles_x * tiles_y + 3) / 4);
+        if (plan == PLAN_TWO_KERNELS) {
+            update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
+            TDK_CUDA(cudaGetLastError());
+            update_depth_search_kernel<<<dim3(qx, 1u, (unsigned)P), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+        } else {
+            a.len_hist = (unsigned int *)(ws + l.len_hist);
+            a.len_cursor = a.len_hist + l.sub * LEN_CLASSES;
+            a.len_class = (unsigned char *)(ws + l.len_class);
+            a.order = (unsigned int *)(ws + l.order);
+            a.rec = (double2 *)(ws + l.rec);
+            a.rec_stride = align_up((size_t)H * W, BLOCK);
+            for (int64_t p0 = 0; p0 < P; p0 += l.sub) {
+                const unsigned ns = (unsigned)(P - p0 < l.sub ? P - p0 : l.sub);
+                a.p0 = (int)p0;
+                if (p0 > 0)   // pair_setup_kernel cleared them for the first sub-batch
+                    TDK_CUDA(cudaMemsetAsync(a.len_hist, 0, (size_t)l.sub * 2 * LEN_CLASSES * sizeof(unsigned int), stream));
+                const dim3 sgrid(qx, 1u, ns);
+                update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
+                update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
+                update_depth_order_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
+                update_depth_match_kernel<<<sgrid, BLOCK, MATCH_SMEM_BYTES, stream>>>(a);
+                TDK_CUDA(cudaGetLastError());
+            }
+        }
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
@@ -935,11 +1287,17 @@ size_t tdk_update_depth_workspace_bytes(int64_t P, int64_t R, int64_t H, int64_t
     return ws_layout(P, R, H, W).total;
 }
 
+size_t tdk_update_depth_workspace_bytes_min(int64_t P, int64_t R, int64_t H, int64_t W)
+{
+    if (P <= 0 || R <= 0 || H <= 0 || W <= 0) return 0;
+    return ws_layout(P, R, H, W, 1).total;
+}
+
 // tuning knob (not part of the reference surface): how update_depth is mapped onto kernels
 int tdk_set_kernel_plan(int plan)
 {
-    if (plan != PLAN_TWO_KERNELS && plan != PLAN_ONE_KERNEL) {
-        tdk_set_error("tdk_set_kernel_plan: %d not in {0,1}", plan);
+    if (plan != PLAN_TWO_KERNELS && plan != PLAN_ONE_KERNEL && plan != PLAN_SORTED) {
+        tdk_set_error("tdk_set_kernel_plan: %d not in {0,1,2}", plan);
         return TDK_ERR_INVALID;
     }
     g_plan = plan;

@@ -70,9 +70,10 @@ def test_c1_single_pair_vga():
     assert_parity(gpu, orc)
 
 
-@pytest.mark.parametrize("plan", [0, 1])
-def test_both_kernel_plans_give_the_oracle_result(plan):
-    """Two kernels with a global candidate queue (default) and one kernel with in-CTA compaction."""
+@pytest.mark.parametrize("plan", [0, 1, 2])
+def test_every_kernel_plan_gives_the_oracle_result(plan):
+    """Sieve + length-sorted line records (2, the default), sieve + per-CTA search over a candidate
+    queue (0), and one kernel with in-CTA compaction (1)."""
     from tadataka_b200 import _lib
     sets = [scene.stack_keyframes([scene.make_pair(1001, H=240, W=320, cam=scene.CAM_VGA / 2)]),
             scene.stack_keyframes([scene.make_keyframe(1002 + i, R=3, H=101, W=147,
@@ -89,7 +90,7 @@ def test_both_kernel_plans_give_the_oracle_result(plan):
             want_d, want_v = _fuse_reference(b, orc)
             assert np.array_equal(fused[0], want_d) and np.array_equal(fused[1], want_v)
     finally:
-        _lib.set_kernel_plan(0)
+        _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
 
 
 def test_c2_keyframe_with_8_references_by_age():
@@ -304,8 +305,8 @@ def test_fused_update_equals_update_then_fusion():
 
 def test_full_size_c2_batch_properties():
     """BASELINE.json configs[1] at the bench's full size (64 VGA keyframes x 8 references): too big
-    for the oracle in a test, so size-independent properties instead -- the two kernel plans (two
-    different kernels) agree bit for bit, a rerun is bit-identical, the flag histogram adds up to
+    for the oracle in a test, so size-independent properties instead -- the three kernel plans (three
+    different sets of kernels) agree bit for bit, a rerun is bit-identical, the flag histogram adds up to
     the pixel count, failed pixels carry their prior -- plus the oracle on three keyframes of the
     batch."""
     import bench
@@ -314,16 +315,19 @@ def test_full_size_c2_batch_properties():
     P, H, W = b["key_img"].shape
     assert (P, H, W) == (64, 480, 640)
     try:
-        _lib.set_kernel_plan(0)
+        _lib.set_kernel_plan(2)
         a0 = _gpu(b, hist=True)
         a1 = _gpu(b, hist=True)
+        _lib.set_kernel_plan(0)
+        b0 = _gpu(b, hist=True)
         _lib.set_kernel_plan(1)
         c0 = _gpu(b, hist=True)
     finally:
-        _lib.set_kernel_plan(0)
-    for x, y, z in zip(a0, a1, c0):
+        _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
+    for x, y, z, w in zip(a0, a1, b0, c0):
         assert np.array_equal(x, y, equal_nan=True), "rerun differs"
-        assert np.array_equal(x, z, equal_nan=True), "kernel plans differ"
+        assert np.array_equal(x, z, equal_nan=True), "kernel plans 2 and 0 differ"
+        assert np.array_equal(x, w, equal_nan=True), "kernel plans 2 and 1 differ"
     d, v, f, am, hist = a0
     assert f.min() >= -9 and f.max() <= 0
     assert int(hist.sum()) == P * H * W
