@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 measurement")
-    ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (0 two kernels, 1 one kernel)")
+    ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (2 sorted [default], 0 two kernels, 1 one kernel)")
     return ap.parse_args()
 
 
@@ -250,6 +250,14 @@ def run_b200(args, rank, world, local_rank):
         _lib.check(_lib.set_kernel_plan(args.plan))
 
     B = args.keyframes
+    plan = args.plan if args.plan >= 0 else _lib.DEFAULT_PLAN
+    # my kernels per resident step: pair_setup + (sorted plan) sieve, lines, order, match per
+    # sub-batch of <= 64 keyframes / (two kernels) sieve, search / (one kernel) tile
+    launches_per_step = {2: 1 + 4 * ((B + 63) // 64), 0: 3, 1: 2}[plan]
+    kernel_desc = {
+        2: "update_depth sieve + lines + order + match kernels (step time, incl. the ~us pair_setup_kernel)",
+        0: "update_depth sieve_kernel + search_kernel (step time, incl. the ~us pair_setup_kernel)",
+        1: "update_depth_tile_kernel (step time, incl. the ~us pair_setup_kernel)"}[plan]
     b = make_workload(rank, B, args.distinct)
     names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
              "prior_variance"]
@@ -406,7 +414,7 @@ def run_b200(args, rank, world, local_rank):
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak, "peak_source": peak_src,
             "traffic": None if traffic_px is None else traffic_px * px_step,
-            "kernel": "update_depth sieve_kernel + search_kernel (step time, incl. the ~us pair_setup_kernel)",
+            "kernel": kernel_desc,
             "algorithmic_bytes_per_px": ALGO_BYTES_PER_PX,
         },
         "clocks": sampler.result(),
@@ -414,7 +422,7 @@ def run_b200(args, rank, world, local_rank):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": 1e3 * e2e_s / e2e_steps,
                 "api": "tdk_update_depth_host (pinned host buffers, fuse_on_success=1)"},
-        "gpu_launches": 3 * args.steps,
+        "gpu_launches": launches_per_step * args.steps,
     }
     if world == 1 and not args.no_cpu_baseline:
         import oracle as ora

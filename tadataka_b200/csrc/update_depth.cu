@@ -838,11 +838,6 @@ constexpr int LEN_CLASSES = 64;
 #define TDK_MATCH_MIN_CTAS 4
 #endif
 constexpr int LINES_MIN_CTAS = TDK_LINES_MIN_CTAS, MATCH_MIN_CTAS = TDK_MATCH_MIN_CTAS;
-#ifndef TDK_MATCH_STAGE
-#define TDK_MATCH_STAGE 0
-#endif
-constexpr int MATCH_STAGE = TDK_MATCH_STAGE;   // line samples staged per thread in shared memory (0 = none)
-constexpr size_t MATCH_SMEM_BYTES = (size_t)MATCH_STAGE * BLOCK * sizeof(double);
 constexpr int REC_DOUBLE2 = 8;   // 128 bytes per queue slot
 constexpr int REC_DOUBLES = 2 * REC_DOUBLE2;
 constexpr int A1_FIELDS = 11;    // ki[5], kstep, gf, gr, idp, prior variance, {ref | pixel}
@@ -883,6 +878,8 @@ __device__ __forceinline__ void record_store(double2 *__restrict__ r, const Line
 __global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kernel(const UpdArgs a)
 {
     __shared__ unsigned int s_hist[10], s_len[LEN_CLASSES];
+    constexpr int REC_PAD = REC_DOUBLE2 + 1;   // 144-byte pitch: 16-byte accesses of a quarter warp hit 32 distinct banks
+    __shared__ double2 s_rec[BLOCK * REC_PAD];
     const int tid = threadIdx.x;
     const int pl = blockIdx.z, p = pl + a.p0;
     const int total = (int)a.cand_count[p];
@@ -915,22 +912,32 @@ __global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kern
             px = t.y;
         }
         __syncthreads();   // every A1 result of this chunk is in registers: the records may overwrite them
-        if (!live) continue;
-        const int x = px & 0xffff, y = px >> 16;
-        const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
-        const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + c.r;
-        LineRec l;
-        const int flag = phase_a2_core(a, pc, xk, yk, v, c, wm1, hm1, l);
-        int cls = 0;
-        if (flag == 1) {
-            cls = min(l.n, LEN_CLASSES - 1);
-            record_store(a.rec + (rec_base + i) * REC_DOUBLE2, l, c.r, px, v);
-            atomicAdd(&s_len[cls], 1u);
-        } else {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
-            a.out_f[map_base + (size_t)y * W + x] = (long long)flag;
-            if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+        if (live) {
+            const int x = px & 0xffff, y = px >> 16;
+            const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
+            const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + c.r;
+            LineRec l;
+            const int flag = phase_a2_core(a, pc, xk, yk, v, c, wm1, hm1, l);
+            int cls = 0;
+            if (flag == 1) {
+                cls = min(l.n, LEN_CLASSES - 1);
+                record_store(s_rec + tid * REC_PAD, l, c.r, px, v);
+                atomicAdd(&s_len[cls], 1u);
+            } else {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
+                a.out_f[map_base + (size_t)y * W + x] = (long long)flag;
+                if (a.hist) atomicAdd(&s_hist[-flag], 1u);
+            }
+            a.len_class[ws_base + i] = (unsigned char)cls;
         }
-        a.len_class[ws_base + i] = (unsigned char)cls;
+        __syncthreads();
+        // the chunk's 256 records are 32 KB of consecutive workspace: copy them out with consecutive
+        // threads on consecutive 16-byte pieces (records of dropped lines are never read)
+        double2 *__restrict__ out = a.rec + (rec_base + first) * REC_DOUBLE2;
+#pragma unroll
+        for (int it = 0; it < REC_DOUBLE2; it++) {
+            const int idx = it * BLOCK + tid;
+            out[idx] = s_rec[(idx >> 3) * REC_PAD + (idx & 7)];
+        }
     }
     __syncthreads();
     if (tid < LEN_CLASSES && s_len[tid]) atomicAdd(&a.len_hist[pl * LEN_CLASSES + tid], s_len[tid]);
@@ -980,10 +987,6 @@ __global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs
 __global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kernel(const UpdArgs a)
 {
     __shared__ unsigned int s_hist[10], s_start[LEN_CLASSES];
-#if TDK_MATCH_STAGE > 0
-    extern __shared__ __align__(16) unsigned char s_dyn[];
-    double *s_stage = reinterpret_cast<double *>(s_dyn);   // [MATCH_STAGE][BLOCK]
-#endif
     const int tid = threadIdx.x, lane = tid & 31;
     const int pl = blockIdx.z, p = pl + a.p0;
     const int W = a.W, H = a.H;
@@ -1001,8 +1004,9 @@ __global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kern
         __syncwarp();   // `item` is warp-uniform: lanes that left the previous item early wait here
         const bool whole_warp = item < nlong;
         const int pos = whole_warp ? item : nlong + (item - nlong) * 32 + lane;
-        if (pos >= nlive) continue;
-        const unsigned int slot = a.order[ws_base + pos];
+        const bool active = pos < nlive;
+        const unsigned int slot = active ? a.order[ws_base + pos] : 0u;
+        if (!active) continue;
         const double2 *__restrict__ r = a.rec + ((size_t)pl * a.rec_stride + slot) * REC_DOUBLE2;
         const double2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4];
         const double2 r7 = r[7];
@@ -1018,30 +1022,12 @@ __global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kern
             double s0 = line_sample(g, 0, a.step, W, H), s1 = line_sample(g, 1, a.step, W, H);
             double s2 = line_sample(g, 2, a.step, W, H), s3 = line_sample(g, 3, a.step, W, H);
             double best = INFINITY;
-#if TDK_MATCH_STAGE > 0
-            // Samples are fetched MATCH_STAGE at a time into a thread-private column of shared memory
-            // (independent loads, so many are in flight at once), then the windows are evaluated from
-            // there in the reference's order: first minimum kept by `e < best`.
-            double *__restrict__ mine = s_stage + tid;
-            for (int next = 4; next < t.n; next += MATCH_STAGE) {
-                const int cnt = min(MATCH_STAGE, t.n - next);
-#pragma unroll 4
-                for (int j = 0; j < cnt; j++) mine[j * BLOCK] = line_sample(g, next + j, a.step, W, H);
-                for (int j = 0; j < cnt; j++) {
-                    const double s4 = mine[j * BLOCK];
-                    const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
-                    if (e < best) { best = e; arg = next + j - 4; }
-                    s0 = s1; s1 = s2; s2 = s3; s3 = s4;
-                }
-            }
-#else
             for (int i = 0; i + 4 < t.n; i++) {
                 const double s4 = line_sample(g, i + 4, a.step, W, H);
                 const double e = window_error(s0, s1, s2, s3, s4, k0, k1, k2, k3, k4);
                 if (e < best) { best = e; arg = i; }
                 s0 = s1; s1 = s2; s2 = s3; s3 = s4;
             }
-#endif
         }
         arg += 2;   // intensities.rs:32-36
         // ---- phase C and the scattered store
@@ -1197,9 +1183,6 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                                       (int)CTA_SMEM_BYTES));
         TDK_CUDA(cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)CTA_SMEM_BYTES));
-        if (MATCH_SMEM_BYTES > 0)
-            TDK_CUDA(cudaFuncSetAttribute(update_depth_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)MATCH_SMEM_BYTES));
         attr_set[dev] = true;
     }
     if (plan == PLAN_ONE_KERNEL) {
@@ -1229,7 +1212,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
                 update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
                 update_depth_order_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
-                update_depth_match_kernel<<<sgrid, BLOCK, MATCH_SMEM_BYTES, stream>>>(a);
+                update_depth_match_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
                 TDK_CUDA(cudaGetLastError());
             }
         }
