@@ -231,6 +231,13 @@ int tdk_transform_dev(const double *T10, const double *ps0, int64_t n, double *p
 int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1, int64_t n,
                         double *depths0, void *stream);
 
+/* Test hook with no counterpart in the reference.  The kernels divide several numerators by one
+ * denominator with nvcc's own division sequence, sharing the part that depends on the denominator
+ * only (tdk_common.cuh, tdk::div2 / tdk::div5).  This runs n pseudo-random cases (seeded; ordinary
+ * magnitudes, arbitrary bit patterns, exponents next to the fast path's limits) through both and
+ * writes to *mismatches (device memory) how many quotients differ from the plain `/`: must be 0. */
+int tdk_selftest_shared_division_dev(int64_t n, uint64_t seed, uint64_t *mismatches, void *stream);
+
 /* ------------------------------------------------------------------ direct pose-change estimation
  * The caller on the other side of the keyframe loop: tadataka/vo/dvo/__init__.py.
  * One Gauss-Newton iteration of _PoseChangeEstimator.__call__ (:76-110) = one

@@ -103,6 +103,58 @@ int check_n(const char *who, int64_t n, bool ptrs_ok)
     return TDK_OK;
 }
 
+
+// ---- self-test of tdk::div2 / tdk::div5 against the plain `/` (tdk_common.cuh) -----------------
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x)
+{
+    x += 0x9e3779b97f4a7c15ULL;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    return x ^ (x >> 31);
+}
+
+// operand classes: 0 = image-like magnitudes, 1 = any bit pattern (NaN, Inf, subnormals included),
+// 2 = exponents next to the limits of the fast path
+__device__ __forceinline__ double test_operand(unsigned long long h, int cls)
+{
+    const unsigned long long mant = h & 0x000fffffffffffffULL, sign = h & 0x8000000000000000ULL;
+    unsigned long long ex;
+    if (cls == 0) ex = 1023 - 40 + (h >> 52) % 80;
+    else if (cls == 1) return __longlong_as_double((long long)h);
+    else {
+        const unsigned long long edges[8] = {0, 1, 2, 54, 0x360, 0x7f7, 0x7fd, 0x7fe};
+        ex = edges[(h >> 52) & 7] + ((h >> 56) & 3);
+        if (ex > 0x7fe) ex = 0x7fe;
+    }
+    return __longlong_as_double((long long)(sign | (ex << 52) | mant));
+}
+
+__global__ void shared_division_selftest_kernel(unsigned long long n, unsigned long long seed,
+                                                unsigned long long *mismatches)
+{
+    unsigned long long bad = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long h = mix64(seed + i * 7);
+        const int cls = (int)(h % 3), cls_b = (int)((h >> 8) % 3);
+        double a[5];
+        for (int j = 0; j < 5; j++) a[j] = test_operand(mix64(h + j + 1), cls);
+        const double b = test_operand(mix64(h + 6), cls_b);
+        double q0, q1;
+        tdk::div2(a[0], a[1], b, q0, q1);
+        double r0 = a[0], r1 = a[1], r2 = a[2], r3 = a[3], r4 = a[4];
+        tdk::div5(r0, r1, r2, r3, r4, b);
+        const double got[7] = {q0, q1, r0, r1, r2, r3, r4};
+        const double want[7] = {a[0] / b, a[1] / b, a[0] / b, a[1] / b, a[2] / b, a[3] / b, a[4] / b};
+        for (int j = 0; j < 7; j++) {
+            const bool nan_g = got[j] != got[j], nan_w = want[j] != want[j];
+            if (nan_g || nan_w) bad += nan_g != nan_w;   // NaN payloads are not compared
+            else bad += __double_as_longlong(got[j]) != __double_as_longlong(want[j]);
+        }
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
 }  // namespace
 
 extern "C" {
@@ -161,6 +213,17 @@ int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1,
     int rc = check_n("tdk_calc_depth0_dev", n, T10 && xs0 && xs1 && depths0);
     if (rc != TDK_OK || n == 0) return rc;
     calc_depth0_kernel<<<blocks_for(n), TPB, 0, (cudaStream_t)stream>>>(T10, xs0, xs1, (size_t)n, depths0);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_selftest_shared_division_dev(int64_t n, uint64_t seed, uint64_t *mismatches, void *stream)
+{
+    if (n < 0 || !mismatches) { tdk_set_error("tdk_selftest_shared_division_dev: bad arguments"); return TDK_ERR_INVALID; }
+    TDK_CUDA(cudaMemsetAsync(mismatches, 0, sizeof(uint64_t), (cudaStream_t)stream));
+    if (n == 0) return TDK_OK;
+    shared_division_selftest_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(
+        (unsigned long long)n, (unsigned long long)seed, (unsigned long long *)mismatches);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

@@ -257,7 +257,7 @@ __device__ __forceinline__ int phase_a1(const UpdArgs &a, const TdkKeyConst &key
     // are tested here.
     double kdx = xk - pc->ex, kdy = yk - pc->ey;
     const double knorm = sqrt(kdx * kdx + kdy * kdy);
-    if (knorm != 0.) { kdx = kdx / knorm; kdy = kdy / knorm; }
+    if (knorm != 0.) tdk::div2(kdx, kdy, knorm, kdx, kdy);
     double kcx[5], kcy[5];
 #pragma unroll
     for (int k = 0; k < 5; k++) {
@@ -335,7 +335,8 @@ __device__ __forceinline__ int phase_a2_core(const UpdArgs &a, const TdkPairCons
     if (g < a.min_grad) return TDK_FLAG_INSUFFICIENT_GRADIENT;
     // ref_coordinates + check_us_ref, epipolar.rs:38-54, semi_dense.rs:62-81
     const double L = sqrt(rdx * rdx + rdy * rdy);
-    const double ux = rdx / (L + TDK_EPS), uy = rdy / (L + TDK_EPS);
+    double ux, uy;
+    tdk::div2(rdx, rdy, L + TDK_EPS, ux, uy);
     const double nf = L / a.step;
     int n = 0;
     if (nf > 0.) n = nf >= 2147483647. ? 2147483647 : (int)nf;   // Rust `as usize`
@@ -353,7 +354,7 @@ __device__ __forceinline__ int phase_a2_core(const UpdArgs &a, const TdkPairCons
     }
     // normalise the key window once (intensities.rs:20 does it for every window)
     const double kn = sqrt(k0 * k0 + k1 * k1 + k2 * k2 + k3 * k3 + k4 * k4);
-    if (kn != 0.) { k0 = k0 / kn; k1 = k1 / kn; k2 = k2 / kn; k3 = k3 / kn; k4 = k4 / kn; }
+    if (kn != 0.) tdk::div5(k0, k1, k2, k3, k4, kn);
     o.k0 = k0; o.k1 = k1; o.k2 = k2; o.k3 = k3; o.k4 = k4;
     o.xminx = xminx; o.xminy = xminy; o.ux = ux; o.uy = uy; o.rdx = rdx; o.rdy = rdy;
     o.g = g; o.kstep = c.kstep; o.n = n;
@@ -406,7 +407,7 @@ __device__ __forceinline__ double window_error(double s0, double s1, double s2, 
 {
     const double wn = sqrt(s0 * s0 + s1 * s1 + s2 * s2 + s3 * s3 + s4 * s4);
     double w0 = s0, w1 = s1, w2 = s2, w3 = s3, w4 = s4;
-    if (wn != 0.) { w0 = s0 / wn; w1 = s1 / wn; w2 = s2 / wn; w3 = s3 / wn; w4 = s4 / wn; }
+    if (wn != 0.) tdk::div5(w0, w1, w2, w3, w4, wn);
     const double d0 = w0 - k0, d1 = w1 - k1, d2 = w2 - k2, d3 = w3 - k3, d4 = w4 - k4;
     return d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
 }
@@ -436,7 +437,8 @@ __device__ __forceinline__ int phase_c_core(const UpdArgs &a, const TdkKeyConst 
 
     // calc_alpha, variance.rs:55-106
     const double rn = sqrt(rdx * rdx + rdy * rdy);
-    const double dhx = rn == 0. ? rdx : rdx / rn, dhy = rn == 0. ? rdy : rdy / rn;
+    double dhx = rdx, dhy = rdy;
+    if (rn != 0.) tdk::div2(rdx, rdy, rn, dhx, dhy);
     double xrefx, xrefy, zz;
     tdk::warp_point(T, xk, yk, depth, xrefx, xrefy, zz);
     const bool bx0 = fabs(dhx) > fabs(dhy);
@@ -462,9 +464,9 @@ __device__ __forceinline__ int phase_c_core(const UpdArgs &a, const TdkKeyConst 
     }
     double lx2 = xk - pc->ptx, ly2 = yk - pc->pty;
     const double ln = sqrt(lx2 * lx2 + ly2 * ly2);
-    if (ln != 0.) { lx2 = lx2 / ln; ly2 = ly2 / ln; }
+    if (ln != 0.) tdk::div2(lx2, ly2, ln, lx2, ly2);
     const double gn = sqrt(gx * gx + gy * gy);
-    if (gn != 0.) { gx = gx / gn; gy = gy / gn; }
+    if (gn != 0.) tdk::div2(gx, gy, gn, gx, gy);
     const double pp = lx2 * gx + ly2 * gy;
     const double geo_var = pp == 0. ? 1. / TDK_EPS : 1. / (pp * pp);
     const double photo_var = 2. / (g / kstep);

@@ -362,3 +362,17 @@ def test_newtsukuba_golden_pair():
     ok = f[0] == 0
     assert np.array_equal(d[0][ok], g["depth_success"])
     assert np.array_equal(v[0][ok], g["variance_success"])
+
+
+def test_shared_denominator_division_is_the_plain_division():
+    """tdk::div2 / tdk::div5 (several numerators, one denominator; tdk_common.cuh) must return what
+    `/` returns, bit for bit: 3 x 20 M seeded cases over ordinary magnitudes, arbitrary bit patterns
+    (NaN, Inf, subnormals) and exponents at the limits of the fast path."""
+    import torch
+    from tadataka_b200 import _lib
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    for seed in (1, 2, 3):
+        _lib.check(_lib.selftest_shared_division_dev(20_000_000, seed, bad.data_ptr(),
+                                                     torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        assert int(bad.item()) == 0, f"seed {seed}: {int(bad.item())} quotients differ from a / b"
