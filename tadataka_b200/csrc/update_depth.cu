@@ -58,6 +58,7 @@ struct UpdArgs {
     size_t rec_stride;          // slots per keyframe in rec: H*W rounded up to whole chunks of 256
     int p0;                     // first keyframe of the sub-batch (blockIdx.z + p0 indexes maps, keys, pairs, cand)
     double vmin, vmax, geo, photo, step, min_grad;
+    double min_grad_sq;         // smallest s with sqrt(s) >= min_grad (NaN if min_grad is NaN)
     int P, R, H, W, tiles_x, tiles_y, fuse;
 };
 
@@ -276,9 +277,11 @@ __device__ __forceinline__ int phase_a1(const UpdArgs &a, const TdkKeyConst &key
     const double g0 = o.ki[1] - o.ki[0], g1 = o.ki[2] - o.ki[1], g2 = o.ki[3] - o.ki[2], g3 = o.ki[4] - o.ki[3];
     const double q0 = g0 * g0, q1 = g1 * g1, q2 = g2 * g2, q3 = g3 * g3;
     const double sf = q0 + q1 + q2 + q3, sr = q3 + q2 + q1 + q0;
+    // sqrt(s) < min_gradient <=> s < min_grad_sq (launch() finds that threshold exactly): the two
+    // square roots are only taken for the pixels that pass
+    if (sf < a.min_grad_sq && sr < a.min_grad_sq) return TDK_FLAG_INSUFFICIENT_GRADIENT;
     const double gf = sqrt(sf);
     const double gr = sr == sf ? gf : sqrt(sr);
-    if (gf < a.min_grad && gr < a.min_grad) return TDK_FLAG_INSUFFICIENT_GRADIENT;
     o.kstep = kstep; o.gf = gf; o.gr = gr; o.idp = idp; o.r = r;
     return 1;
 }
@@ -1100,6 +1103,21 @@ WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W, int64_t sub = SUB
     return l;
 }
 
+// The smallest double s >= 0 with sqrt(s) >= m, so that `sqrt(s) < m` and `s < threshold` are the same
+// test for every s (IEEE sqrt is correctly rounded, hence monotone; the host's sqrt and the
+// device's agree).  m <= 0: sqrt(s) < m never holds -> 0; m = NaN -> NaN (both tests always false).
+double sqrt_threshold(double m)
+{
+    if (m != m) return m;
+    if (m <= 0.) return 0.;
+    if (m > 1.7976931348623157e308) return m;   // +inf: sqrt(s) < inf <=> s < inf
+    double s = m * m;
+    if (s > 1.7976931348623157e308) s = 1.7976931348623157e308;
+    while (s > 0. && sqrt(s) >= m) s = nextafter(s, 0.);
+    while (sqrt(s) < m) s = nextafter(s, INFINITY);
+    return s;
+}
+
 enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
 int g_plan = PLAN_SORTED;
 
@@ -1175,6 +1193,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmin = 1. / (params[1] + TDK_EPS_INV);
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
+    a.min_grad_sq = sqrt_threshold(a.min_grad);
     a.p0 = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr; a.len_hist = nullptr; a.len_cursor = nullptr;
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
     static bool attr_set[64] = {};
