@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 measurement")
+    ap.add_argument("--device-scenes", action="store_true",
+                    help="render every keyframe's world on the GPU (tdk_render_scene_dev) instead of in numpy")
     ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (2 sorted [default], 0 two kernels, 1 one kernel)")
     return ap.parse_args()
 
@@ -258,11 +260,21 @@ def run_b200(args, rank, world, local_rank):
         2: "update_depth sieve + lines + order + match kernels (step time, incl. the ~us pair_setup_kernel)",
         0: "update_depth sieve_kernel + search_kernel (step time, incl. the ~us pair_setup_kernel)",
         1: "update_depth_tile_kernel (step time, incl. the ~us pair_setup_kernel)"}[plan]
-    b = make_workload(rank, B, args.distinct)
     names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
              "prior_variance"]
-    pinned = {k: torch.from_numpy(b[k]).pin_memory() for k in names}
-    t = {k: pinned[k].to(dev, non_blocking=True) for k in names}
+    if args.device_scenes:
+        # every keyframe its own world, rendered by the CUDA ray-caster (csrc/scene.cu); the host
+        # copies below only feed the e2e leg and the CPU baseline
+        from tadataka_b200 import scene_device
+        t = scene_device.make_keyframes([2000 + 1000 * rank + i for i in range(B)], R=R, H=H, W=W, device=dev)
+        b = {k: t[k].cpu().numpy() for k in names}
+        b["age"] = b["age"].astype(np.uint64)
+        b["params"] = t["params"]
+        pinned = {k: torch.from_numpy(b[k]).pin_memory() for k in names}
+    else:
+        b = make_workload(rank, B, args.distinct)
+        pinned = {k: torch.from_numpy(b[k]).pin_memory() for k in names}
+        t = {k: pinned[k].to(dev, non_blocking=True) for k in names}
     params = np.ascontiguousarray(b["params"], dtype=np.float64)
     out = (torch.empty((B, H, W), dtype=torch.float64, device=dev),
            torch.empty((B, H, W), dtype=torch.float64, device=dev),
@@ -403,7 +415,9 @@ def run_b200(args, rank, world, local_rank):
         "config": {
             "workload": f"C2: {B} x (640x480 keyframe vs 8 reference frames by age + Gaussian "
                         "fusion) per GPU per step",
-            "keyframes_per_gpu": B, "refs": R, "distinct_scenes": min(args.distinct, B),
+            "keyframes_per_gpu": B, "refs": R,
+            "distinct_scenes": B if args.device_scenes else min(args.distinct, B),
+            "scenes": "CUDA ray-caster" if args.device_scenes else "numpy ray-caster",
             "l2": f"inputs {h2d / 1e9:.2f} GB per step >> 126 MB L2 (no flush needed)",
             "success_px_per_step": n_success, "success_px_per_s": world * n_success / (ms_step * 1e-3),
             "params": [float(x) for x in params], "e2e_matches_resident": same,

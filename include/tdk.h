@@ -231,6 +231,17 @@ int tdk_transform_dev(const double *T10, const double *ps0, int64_t n, double *p
 int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1, int64_t n,
                         double *depths0, void *stream);
 
+/* Synthetic-scene ray-caster (SURVEY 8d workload, 8f rank 3); no counterpart in the reference,
+ * which reads its frames from datasets.  Renders N views of one piecewise-planar world, one thread
+ * per pixel, without any graphics API: the device version of tadataka_b200/scene.py World.render.
+ *   planes [K,14] = p0[3], normal[3], a[3], b[3], half_a, half_b (inf = unbounded)
+ *   tex [K,5] = fa, fb, phase1, phase2, noise frequency     lattice [K,64,64] value-noise lattice
+ *   z0: depth reported where no plane is hit     T_wc [N,16] camera-to-world poses, cams [N,4]
+ *   image, depth [N,H,W] f64: intensity in [0,1] and z in the camera frame (exact ground truth) */
+int tdk_render_scene_dev(const double *planes, const double *tex, const double *lattice, int64_t K,
+                         double z0, const double *T_wc, const double *cams, int64_t N, int64_t H,
+                         int64_t W, double *image, double *depth, void *stream);
+
 /* Test hook with no counterpart in the reference.  The kernels divide several numerators by one
  * denominator with nvcc's own division sequence, sharing the part that depends on the denominator
  * only (tdk_common.cuh, tdk::div2 / tdk::div5).  This runs n pseudo-random cases (seeded; ordinary
