@@ -200,6 +200,14 @@ int tdk_increment_age_dev(const uint64_t *age0, const double *cam0, const double
                           const double *T10, const double *depth0, int64_t P, int64_t H, int64_t W,
                           uint64_t *age1, void *workspace, size_t workspace_bytes, void *stream);
 
+/* Reference-frame pruning.  update_depth reads refframes[len - age], so a frame
+ * is needed exactly as long as some pixel carries the matching age; the reference's loop leaves the
+ * clean-up as a TODO (examples/semi_dense_vo.py:202) and keeps every frame.  counts [P, max_age+2]
+ * u64 receives, per keyframe, the number of pixels of each age 0..max_age and, in the last bin, of
+ * all older ones; the caller drops the frames older than the largest age in use. */
+int tdk_age_usage_dev(const uint64_t *age, int64_t P, int64_t H, int64_t W, int64_t max_age,
+                      uint64_t *counts, void *stream);
+
 /* rust_bindings.semi_dense.propagate (src/py/semi_dense.rs:189-218 ->
  * src/semi_dense/propagation.rs:48-92) for P independent frames.  Collisions are folded in raster
  * order of the source pixel, as the reference's loop does.

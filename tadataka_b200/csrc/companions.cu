@@ -413,6 +413,36 @@ int check_frames(const char *who, int64_t P, int64_t H, int64_t W)
     return TDK_OK;
 }
 
+
+// How many pixels of each keyframe carry each age, ages above max_age pooled in the last bin:
+// the information the caller's "remove unused reference frames" step needs
+// (examples/semi_dense_vo.py:202, a TODO there).  Warp-aggregated shared-memory counts for small
+// bin counts, global atomics beyond.
+constexpr int AGE_BINS_SMEM = 1024;
+__global__ void __launch_bounds__(256) age_usage_kernel(const uint64_t *__restrict__ age, int hw, int bins,
+                                                       unsigned long long *__restrict__ counts)
+{
+    __shared__ unsigned int s_cnt[AGE_BINS_SMEM];
+    const int p = blockIdx.y;
+    const bool in_smem = bins <= AGE_BINS_SMEM;
+    if (in_smem) {
+        for (int i = threadIdx.x; i < bins; i += blockDim.x) s_cnt[i] = 0;
+        __syncthreads();
+    }
+    unsigned long long *out = counts + (size_t)p * bins;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < hw; i += gridDim.x * blockDim.x) {
+        const uint64_t a = age[(size_t)p * hw + i];
+        const int b = a < (uint64_t)(bins - 1) ? (int)a : bins - 1;
+        if (in_smem) atomicAdd(&s_cnt[b], 1u);
+        else atomicAdd(&out[b], 1ULL);
+    }
+    if (in_smem) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < bins; i += blockDim.x)
+            if (s_cnt[i]) atomicAdd(&out[i], (unsigned long long)s_cnt[i]);
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -478,6 +508,27 @@ int tdk_increment_age_dev(const uint64_t *age0, const double *cam0, const double
     age_scatter_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, (int)H, (int)W, winner);
     TDK_CUDA(cudaGetLastError());
     age_gather_kernel<<<grid, TPB, 0, st>>>(age0, winner, hw, age1);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_age_usage_dev(const uint64_t *age, int64_t P, int64_t H, int64_t W, int64_t max_age, uint64_t *counts,
+                      void *stream)
+{
+    if (!age || !counts) { tdk_set_error("tdk_age_usage_dev: null pointer argument"); return TDK_ERR_INVALID; }
+    int rc = check_frames("tdk_age_usage_dev", P, H, W);
+    if (rc != TDK_OK) return rc;
+    if (max_age < 0 || max_age > (1 << 24)) {
+        tdk_set_error("tdk_age_usage_dev: max_age %lld not in [0, 2^24]", (long long)max_age);
+        return TDK_ERR_INVALID;
+    }
+    const int bins = (int)max_age + 2;   // ages 0..max_age, then "older"
+    cudaStream_t st = (cudaStream_t)stream;
+    TDK_CUDA(cudaMemsetAsync(counts, 0, (size_t)P * bins * sizeof(uint64_t), st));
+    const int hw = (int)(H * W);
+    int blocks = (hw + 256 * 8 - 1) / (256 * 8);
+    if (blocks > 296) blocks = 296;
+    age_usage_kernel<<<dim3((unsigned)blocks, (unsigned)P), 256, 0, st>>>(age, hw, bins, (unsigned long long *)counts);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

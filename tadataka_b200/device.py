@@ -323,3 +323,21 @@ def calc_depth0(T10, xs0, xs1):
         out = torch.empty((n,), dtype=_F64, device=xs0.device)
         _lib.check(_lib.calc_depth0_dev(_ptr(T10), _ptr(xs0), _ptr(xs1), n, _ptr(out), _stream()))
     return out
+
+
+def age_usage(age, max_age):
+    """Pixels per age value: age [P,H,W] (or [H,W]) -> int64 tensor [P, max_age + 2] (or
+    [max_age + 2]); bin k < max_age + 1 counts age == k, the last bin every older pixel.
+    What a caller needs to drop reference frames no pixel points to any more
+    (examples/semi_dense_vo.py:202 leaves that as a TODO)."""
+    _require_cuda()
+    squeeze = age.dim() == 2
+    a = age.unsqueeze(0) if squeeze else age
+    _chk(a, "age", torch.uint64)
+    if a.dim() != 3:
+        raise ValueError("age must be [P,H,W] or [H,W]")
+    P, H, W = a.shape
+    with torch.cuda.device(a.device):
+        counts = torch.empty((P, int(max_age) + 2), dtype=torch.int64, device=a.device)
+        _lib.check(_lib.age_usage_dev(_ptr(a), P, H, W, int(max_age), _ptr(counts), _stream()))
+    return counts[0] if squeeze else counts

@@ -25,7 +25,8 @@ def _cu(a, dtype=np.float64):
 
 class SemiDenseMapper:
     def __init__(self, camera_params, image, transform_wf, params, default_depth, default_variance,
-                 uncertaintity_bias, depth_map=None, variance_map=None, fuse=False, regularize=False):
+                 uncertaintity_bias, depth_map=None, variance_map=None, fuse=False, regularize=False,
+                 prune=False):
         """First frame: age 0 everywhere; depth defaults to `default_depth`, variance to
         `default_variance` (semi_dense_vo.py:210-219 draws the depth at random instead: pass it)."""
         device._require_cuda()
@@ -36,6 +37,7 @@ class SemiDenseMapper:
         self.default_depth, self.default_variance = float(default_depth), float(default_variance)
         self.bias = float(uncertaintity_bias)
         self.fuse, self.smooth = bool(fuse), bool(regularize)
+        self.prune = bool(prune)   # drop reference frames no pixel's age points to any more
         self.depth = _cu(np.full((H, W), self.default_depth) if depth_map is None else depth_map)
         self.variance = _cu(np.full((H, W), self.default_variance) if variance_map is None
                             else variance_map)
@@ -76,7 +78,24 @@ class SemiDenseMapper:
         self._cams.append(cam1)
         self._poses.append(T_w1)
         assert len(self._images) == R + 1
+        if self.prune:
+            self._drop_unused_frames()
         return f
+
+    def _drop_unused_frames(self):
+        """The reference's TODO (examples/semi_dense_vo.py:202).  update_depth reads
+        refframes[len - age], so the frames older than the largest age on the map are dead; dropping
+        them from the front leaves len - age pointing at the same frames.  The current frame always
+        stays (the next increment_age needs its pose and camera)."""
+        n = len(self._images)
+        counts = device.age_usage(self.age, n).cpu().numpy()   # ages 0..n, then older (impossible)
+        used = np.nonzero(counts)[0]
+        oldest = int(used.max()) if used.size else 0
+        # at the next track() the ages have grown by one and the list by one: frame index
+        # (n + 1) - (oldest + 1) = n - oldest is the oldest one still read
+        keep_from = max(0, min(n - 1 - oldest, n - 1))
+        if keep_from > 0:
+            del self._images[:keep_from], self._cams[:keep_from], self._poses[:keep_from]
 
     def maps(self):
         """(depth, variance, age, flag) as numpy arrays (one device -> host copy each)."""

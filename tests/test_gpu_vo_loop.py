@@ -112,3 +112,35 @@ def test_mapper_runs_the_same_loop():
         assert np.array_equal(depth, o_depth) and np.array_equal(var, o_var)
         assert np.array_equal(age, o_age)
     assert m.n_frames == n_frames
+
+
+def test_pruning_unused_reference_frames_changes_nothing_but_the_memory():
+    """SemiDenseMapper(prune=True) drops the reference frames no pixel's age points to any more
+    (the reference's TODO, examples/semi_dense_vo.py:202): same maps as the mapper that keeps
+    every frame, fewer frames held once old pixels have left the map."""
+    from rust_bindings.camera import CameraParameters
+    from tadataka_b200 import device
+    from tadataka_b200.mapper import SemiDenseMapper
+    H, W, n_frames = 96, 128, 9
+    cam = np.array([100.0, 100.0, 63.5, 47.5])
+    frames, cam, params = scene.make_sequence(3200, n_frames=n_frames, H=H, W=W, cam=cam)
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    depth0 = np.random.default_rng(3200).uniform(params[0], params[1], (H, W))
+    keep = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0)
+    lean = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0,
+                           prune=True)
+    for i in range(1, n_frames):
+        img1, T_w1, _ = frames[i]
+        keep.track(cp, img1, T_w1)
+        lean.track(cp, img1, T_w1)
+        for a, b in zip(keep.maps(), lean.maps()):
+            assert np.array_equal(a, b, equal_nan=True)
+        counts = device.age_usage(keep.age, i).cpu().numpy()
+        assert counts.sum() == H * W and counts[-1] == 0
+        assert np.array_equal(counts[:-1], np.bincount(keep.maps()[2].ravel().astype(np.int64), minlength=i + 1))
+        if i == 4:   # a re-initialisation: every pixel young again, in both mappers
+            for m in (keep, lean):
+                m.age = torch.clamp(m.age.to(torch.int64), max=1).to(torch.uint64)
+            lean._drop_unused_frames()
+            assert lean.n_frames == 2 and keep.n_frames == 5
+    assert lean.n_frames < keep.n_frames == n_frames
