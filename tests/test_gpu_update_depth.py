@@ -376,3 +376,26 @@ def test_shared_denominator_division_is_the_plain_division():
                                                      torch.cuda.current_stream().cuda_stream))
         torch.cuda.synchronize()
         assert int(bad.item()) == 0, f"seed {seed}: {int(bad.item())} quotients differ from a / b"
+
+
+def test_smallest_accepted_workspace_gives_the_same_maps(monkeypatch):
+    """tdk_update_depth_workspace_bytes_min: one keyframe per sub-batch of the sorted plan instead
+    of up to 64 -- more launches, identical results; one byte less is refused."""
+    import torch
+    from tadataka_b200 import _lib, device
+    b = scene.stack_keyframes([scene.make_keyframe(2600 + i, R=2, H=96, W=128, cam=scene.CAM_VGA / 5)
+                               for i in range(5)])
+    want = _gpu(b, hist=True)
+    P, H, W = b["key_img"].shape
+    small = _lib.update_depth_workspace_bytes_min(P, 2, H, W)
+    assert 0 < small < _lib.update_depth_workspace_bytes(P, 2, H, W)
+    device._workspaces.clear()
+    monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small)
+    got = _gpu(b, hist=True)
+    for x, y in zip(want, got):
+        assert np.array_equal(x, y, equal_nan=True)
+    device._workspaces.clear()
+    monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small - 1)
+    with pytest.raises(_lib.TdkError, match="workspace"):
+        _gpu(b)
+    device._workspaces.clear()
