@@ -399,3 +399,24 @@ def test_smallest_accepted_workspace_gives_the_same_maps(monkeypatch):
     with pytest.raises(_lib.TdkError, match="workspace"):
         _gpu(b)
     device._workspaces.clear()
+
+
+@pytest.mark.parametrize("min_gradient", [0.0, -1.0, 1e-200, 1e-3, 0.05, 0.2, 0.7, 1.5, 1e200, float("inf"),
+                                          float("nan"), 0.2 * (1 + 2 ** -52), 0.2 * (1 - 2 ** -53)])
+def test_gradient_threshold_without_square_roots_matches_the_oracle(min_gradient):
+    """The sieve tests s < T instead of sqrt(s) < min_gradient, T found on the host: every kind of
+    threshold (non-positive, tiny, ordinary, neighbours of an ordinary one, huge, inf, NaN) must
+    give the oracle's flags and maps bit for bit, in every plan."""
+    from tadataka_b200 import _lib
+    b = scene.stack_keyframes([scene.make_keyframe(2700, R=2, H=96, W=128, cam=scene.CAM_VGA / 5)])
+    b["params"] = b["params"].copy()
+    b["params"][5] = min_gradient
+    orc = _oracle(b)
+    try:
+        for plan in (2, 0, 1):
+            _lib.set_kernel_plan(plan)
+            gpu = _gpu(b)
+            for x, y in zip(gpu[:4], orc[:4]):
+                assert np.array_equal(x, y, equal_nan=True), f"plan {plan}"
+    finally:
+        _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
