@@ -420,3 +420,39 @@ def test_gradient_threshold_without_square_roots_matches_the_oracle(min_gradient
                 assert np.array_equal(x, y, equal_nan=True), f"plan {plan}"
     finally:
         _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
+
+
+def test_update_depth_replays_from_a_cuda_graph():
+    """The launch is memset nodes and kernels on the caller's stream only, so it can be captured once
+    and replayed: the replay must write the maps an eager call writes, also after the inputs changed
+    in place."""
+    import torch
+    from tadataka_b200 import device
+    items = [scene.make_keyframe(2800 + i, R=3, H=96, W=128, cam=scene.CAM_VGA / 5) for i in range(3)]
+    b = scene.stack_keyframes(items)
+    t = _dev(b)
+    args = [t[k] for k in ("key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
+                           "prior_variance")]
+    P, H, W = b["key_img"].shape
+    out = (torch.empty((P, H, W), dtype=torch.float64, device="cuda"),
+           torch.empty((P, H, W), dtype=torch.float64, device="cuda"),
+           torch.empty((P, H, W), dtype=torch.int64, device="cuda"))
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        device.update_depth(*args, b["params"], check=False, out=out, fuse=True)   # allocates the workspace
+        side.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            device.update_depth(*args, b["params"], check=False, out=out, fuse=True)
+    for trial in range(2):
+        for o in out:
+            o.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        want = device.update_depth(*args, b["params"], fuse=True)
+        torch.cuda.synchronize()
+        for x, y in zip(out, want):
+            assert torch.equal(x, y) or np.array_equal(x.cpu().numpy(), y.cpu().numpy(), equal_nan=True)
+        assert int((out[2] == 0).sum()) > 20
+        # new priors in the same buffers: the graph must pick them up
+        t["prior_variance"].mul_(0.5)
