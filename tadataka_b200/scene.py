@@ -161,21 +161,28 @@ def stack_keyframes(items):
     return out
 
 
-def make_sequence(seed, n_frames=30, H=480, W=640, cam=None, pset=SET_S):
-    """C3-style input: frames on a smooth seeded trajectory with ground-truth poses.
-    -> list of (image, T_wf, gt_depth), camera vector, params."""
-    cam = CAM_VGA if cam is None else np.asarray(cam, dtype=np.float64)
+def sequence_poses(seed, n_frames=30, pset=SET_S):
+    """The smooth seeded trajectory of make_sequence: n_frames camera-to-world poses [n,4,4]."""
     rng = np.random.default_rng(seed)
-    world = World(pset, seed)
     base = pset["baseline"]
     vel = np.array([base * 0.5, base * 0.05, base * 0.15])
     phase = rng.uniform(0, 6.28, size=3)
-    frames = []
+    poses = []
     for i in range(n_frames):
         t = vel * i + 0.2 * base * np.sin(0.3 * i + phase)
         Rm = rotation(np.deg2rad(0.3 * np.sin(0.2 * i + phase[0])), np.deg2rad(0.15 * i * 0.3),
                       np.deg2rad(0.2 * np.sin(0.25 * i + phase[2])))
-        T_wf = pose(Rm, t)
+        poses.append(pose(Rm, t))
+    return np.stack(poses)
+
+
+def make_sequence(seed, n_frames=30, H=480, W=640, cam=None, pset=SET_S):
+    """C3-style input: frames on a smooth seeded trajectory with ground-truth poses.
+    -> list of (image, T_wf, gt_depth), camera vector, params."""
+    cam = CAM_VGA if cam is None else np.asarray(cam, dtype=np.float64)
+    world = World(pset, seed)
+    frames = []
+    for T_wf in sequence_poses(seed, n_frames, pset):
         img, gt = world.render(T_wf, cam, H, W)
         frames.append((img, T_wf, gt))
     return frames, cam.copy(), np.array(pset["params"], dtype=np.float64)
