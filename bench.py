@@ -252,7 +252,7 @@ def run_b200(args, rank, world, local_rank):
         _lib.check(_lib.set_kernel_plan(args.plan))
 
     B = args.keyframes
-    plan = args.plan if args.plan >= 0 else _lib.DEFAULT_PLAN
+    plan = args.plan if args.plan >= 0 else (0 if B * H * W <= 640 * 480 else 2)   # what -1 (automatic) resolves to
     # my kernels per resident step: pair_setup + (sorted plan) sieve, lines, order, match per
     # sub-batch of <= 64 keyframes / (two kernels) sieve, search / (one kernel) tile
     launches_per_step = {2: 1 + 4 * ((B + 63) // 64), 0: 3, 1: 2}[plan]

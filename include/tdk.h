@@ -149,11 +149,12 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 void *stream);
 
 /* Tuning knob with no counterpart in the reference: how update_depth is mapped onto kernels.
- * 2 (default) = a sieve over all pixels that queues the survivors of the gradient test in the
- * workspace, a kernel that sets up their search lines, a counting sort of the lines by length, and a
- * search kernel in which every warp walks 32 lines of equal length; 0 = the sieve, then one search
- * kernel over 256 queued pixels per CTA (smaller workspace: 4 bytes per pixel); 1 = one kernel, each
- * CTA compacts and searches its own 64x4 tile (what tdk_update_depth_static_dev runs).
+ * 2 = a sieve over all pixels that queues the survivors of the gradient test in the workspace, a
+ * kernel that sets up their search lines, a counting sort of the lines by length, and a search
+ * kernel in which every warp walks 32 lines of equal length; 0 = the sieve, then one search kernel
+ * over 256 queued pixels per CTA (smaller workspace: 4 bytes per pixel); 1 = one kernel, each CTA
+ * compacts and searches its own 64x4 tile (what tdk_update_depth_static_dev runs); -1 (default) =
+ * 0 for launches of at most 640x480 pixels in total, 2 for larger ones.
  * Results do not depend on it. */
 int tdk_set_kernel_plan(int plan);
 

@@ -36,7 +36,7 @@ def _sig(name, restype, *argtypes):
 last_error = _sig("tdk_last_error", C.c_char_p)
 version = _sig("tdk_version", C.c_char_p)
 set_kernel_plan = _sig("tdk_set_kernel_plan", C.c_int, C.c_int)
-DEFAULT_PLAN = 2   # sieve + length-sorted line records (update_depth.cu)
+DEFAULT_PLAN = -1  # automatic: sorted line records (2) except for single small keyframes (0); update_depth.cu
 update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64, I64, I64)
 update_depth_workspace_bytes_min = _sig("tdk_update_depth_workspace_bytes_min", SZ, I64, I64, I64, I64)
 update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,

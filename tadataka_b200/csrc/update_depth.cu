@@ -56,6 +56,7 @@ struct UpdArgs {
     unsigned int *len_hist;     // [S, 64] lines per length class
     unsigned int *len_cursor;   // [S, 64] slots handed out per class while `order` is filled
     size_t rec_stride;          // slots per keyframe in rec: H*W rounded up to whole chunks of 256
+    int warp_budget;            // match_kernel: warps per keyframe that can be resident at once
     int p0;                     // first keyframe of the sub-batch (blockIdx.z + p0 indexes maps, keys, pairs, cand)
     double vmin, vmax, geo, photo, step, min_grad;
     double min_grad_sq;         // smallest s with sqrt(s) >= min_grad (NaN if min_grad is NaN)
@@ -999,8 +1000,19 @@ __global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kern
     if (tid < 10) s_hist[tid] = 0;
     class_starts(a.len_hist + pl * LEN_CLASSES, s_start, tid);
     __syncthreads();
-    const int nlong = (int)s_start[LEN_CLASSES - 2];   // lines of class 63 come first
     const int nlive = (int)s_start[0];                 // class 0 (dropped lines) would start here
+    // Lines of class >= whole come first in `order` and take a whole warp each.  Class 63 always
+    // does; when the launch is small enough to leave warps idle (a.warp_budget warps per keyframe
+    // can be resident at once), shorter lines do too, longest first, as far as the budget goes:
+    // the search of a single keyframe is a latency chain, and a 40-sample line walked by one lane
+    // is 20 times longer than the same line walked by a warp.
+    int whole = LEN_CLASSES - 1;
+    while (whole > 8) {
+        const int nl = (int)s_start[whole - 2];   // lines of class >= whole - 1
+        if (nl + (nlive - nl + 31) / 32 > a.warp_budget) break;
+        whole--;
+    }
+    const int nlong = (int)s_start[whole - 1];
     const int nitems = nlong + (nlive - nlong + 31) / 32;
     const TdkKeyConst key = a.keys[p];
     const int warps = BLOCK / 32;
@@ -1118,8 +1130,16 @@ double sqrt_threshold(double m)
     return s;
 }
 
-enum { PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
-int g_plan = PLAN_SORTED;
+enum { PLAN_AUTO = -1, PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
+int g_plan = PLAN_AUTO;
+
+// The sorted plan pays two more launches and a trip of the line records through the workspace; a
+// launch of a single VGA-sized keyframe is too small to earn that back (50 against 57 us).
+int resolve_plan(int plan, int64_t P, int64_t H, int64_t W)
+{
+    if (plan != PLAN_AUTO) return plan;
+    return P * H * W <= 640 * 480 ? PLAN_TWO_KERNELS : PLAN_SORTED;
+}
 
 
 int launch(const double *key_imgs, const double *const *key_ptrs_host, const double *key_cams,
@@ -1194,11 +1214,17 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
     a.min_grad_sq = sqrt_threshold(a.min_grad);
-    a.p0 = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr; a.len_hist = nullptr; a.len_cursor = nullptr;
+    a.p0 = 0; a.warp_budget = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr; a.len_hist = nullptr; a.len_cursor = nullptr;
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
     static bool attr_set[64] = {};
+    static int sm_counts[64] = {};
     int dev = 0;
     TDK_CUDA(cudaGetDevice(&dev));
+    int sm_count = 148;
+    if (dev >= 0 && dev < 64) {
+        if (!sm_counts[dev]) TDK_CUDA(cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev));
+        sm_count = sm_counts[dev];
+    }
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
         TDK_CUDA(cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)CTA_SMEM_BYTES));
@@ -1230,10 +1256,13 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 if (p0 > 0)   // pair_setup_kernel cleared them for the first sub-batch
                     TDK_CUDA(cudaMemsetAsync(a.len_hist, 0, (size_t)l.sub * 2 * LEN_CLASSES * sizeof(unsigned int), stream));
                 const dim3 sgrid(qx, 1u, ns);
+                // 32 resident warps per SM at match_kernel's 64 registers
+                a.warp_budget = (int)((int64_t)sm_count * 32 / ns);
+                const unsigned mx = (unsigned)((a.warp_budget + BLOCK / 32 - 1) / (BLOCK / 32));
                 update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
                 update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
                 update_depth_order_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
-                update_depth_match_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
+                update_depth_match_kernel<<<dim3(mx > qx ? mx : qx, 1u, ns), BLOCK, 0, stream>>>(a);
                 TDK_CUDA(cudaGetLastError());
             }
         }
@@ -1300,8 +1329,8 @@ size_t tdk_update_depth_workspace_bytes_min(int64_t P, int64_t R, int64_t H, int
 // tuning knob (not part of the reference surface): how update_depth is mapped onto kernels
 int tdk_set_kernel_plan(int plan)
 {
-    if (plan != PLAN_TWO_KERNELS && plan != PLAN_ONE_KERNEL && plan != PLAN_SORTED) {
-        tdk_set_error("tdk_set_kernel_plan: %d not in {0,1,2}", plan);
+    if (plan != PLAN_AUTO && plan != PLAN_TWO_KERNELS && plan != PLAN_ONE_KERNEL && plan != PLAN_SORTED) {
+        tdk_set_error("tdk_set_kernel_plan: %d not in {-1,0,1,2}", plan);
         return TDK_ERR_INVALID;
     }
     g_plan = plan;
@@ -1318,7 +1347,8 @@ int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const d
 {
     return launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, g_plan, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan, P, H, W), workspace, workspace_bytes,
+                  (cudaStream_t)stream);
 }
 
 int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double *key_cams,
@@ -1332,7 +1362,8 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
 {
     return launch(nullptr, key_img_ptrs, key_cams, T_wk, nullptr, ref_img_ptrs, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, g_plan, workspace, workspace_bytes, (cudaStream_t)stream);
+                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan, P, H, W), workspace, workspace_bytes,
+                  (cudaStream_t)stream);
 }
 
 int tdk_update_depth_status(const void *workspace, void *stream)

@@ -23,6 +23,15 @@ def _cu(a, dtype=np.float64):
     return torch.from_numpy(np.ascontiguousarray(a, dtype=dtype)).cuda()
 
 
+def _upload(a):
+    """numpy f64 array -> device tensor through pinned memory (torch's caching host allocator), so
+    the copy is asynchronous and the host goes on preparing the next launch."""
+    src = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64))
+    pinned = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
+    pinned.copy_(src)
+    return pinned.cuda(non_blocking=True)
+
+
 class SemiDenseMapper:
     def __init__(self, camera_params, image, transform_wf, params, default_depth, default_variance,
                  uncertaintity_bias, depth_map=None, variance_map=None, fuse=False, regularize=False,
@@ -46,6 +55,7 @@ class SemiDenseMapper:
         self._images = [_cu(image)]
         self._cams = [camera_vector(camera_params)]
         self._poses = [np.ascontiguousarray(transform_wf, dtype=np.float64)]
+        self._pending = None   # age census of the last map, on its way to the host
 
     @property
     def n_frames(self):
@@ -60,16 +70,23 @@ class SemiDenseMapper:
             raise ValueError("every frame must have the first frame's shape")
         cam1 = camera_vector(camera_params)
         T_w1 = np.ascontiguousarray(transform_wf, dtype=np.float64)
+        self._apply_pending_prune()
         cam0, T_w0 = self._cams[-1], self._poses[-1]
         T10 = np.linalg.inv(T_w1) @ T_w0            # semi_dense_vo.py: transform10
-        g_T10, g_cam0, g_cam1 = _cu(T10), _cu(cam0), _cu(cam1)
+        R = len(self._images)
+        # one pinned staging buffer and one copy for the frame's small operands, one for the image
+        small = np.concatenate([T10.ravel(), cam0, cam1, T_w1.ravel(), np.concatenate(self._cams),
+                                np.concatenate([p.ravel() for p in self._poses])])
+        g_small = _upload(small)
+        g_T10, g_cam0, g_cam1 = g_small[0:16].view(4, 4), g_small[16:20], g_small[20:24]
+        g_Tw1 = g_small[24:40].view(4, 4)
+        g_cams = g_small[40:40 + 4 * R].view(R, 4)
+        g_poses = g_small[40 + 4 * R:40 + 20 * R].view(R, 4, 4)
+        g_img = _upload(image)
         age1 = device.increment_age(self.age, g_cam0, g_cam1, g_T10, self.depth)
         depth1, var1 = device.propagate(g_T10, g_cam0, g_cam1, self.depth, self.variance,
                                         self.default_depth, self.default_variance, self.bias)
-        g_img = _cu(image)
-        R = len(self._images)
-        d, v, f = device.update_depth_frames(g_img, g_cam1, _cu(T_w1), self._images,
-                                             _cu(np.stack(self._cams)), _cu(np.stack(self._poses)),
+        d, v, f = device.update_depth_frames(g_img, g_cam1, g_Tw1, self._images, g_cams, g_poses,
                                              age1, depth1, var1, self.params, fuse=self.fuse)
         if self.smooth:
             d = device.regularize(d, v, f)
@@ -79,20 +96,44 @@ class SemiDenseMapper:
         self._poses.append(T_w1)
         assert len(self._images) == R + 1
         if self.prune:
-            self._drop_unused_frames()
+            self._count_ages()
         return f
 
+    def _count_ages(self):
+        """Launch the age census of the new map and start its copy to pinned host memory; the
+        pruning it allows is applied at the start of the next track(), so no frame waits for it."""
+        n = len(self._images)
+        counts = device.age_usage(self.age, n)
+        host = torch.empty(counts.shape, dtype=counts.dtype, pin_memory=True)
+        host.copy_(counts, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+        self._pending = (host, done, n)
+
+    def _apply_pending_prune(self):
+        if self._pending is None:
+            return
+        host, done, n = self._pending
+        self._pending = None
+        done.synchronize()
+        self._drop_frames_older_than(host.numpy(), n)
+
     def _drop_unused_frames(self):
+        """Census and pruning in one step (waits for the device)."""
+        n = len(self._images)
+        self._pending = None
+        self._drop_frames_older_than(device.age_usage(self.age, n).cpu().numpy(), n)
+
+    def _drop_frames_older_than(self, counts, n):
         """The reference's TODO (examples/semi_dense_vo.py:202).  update_depth reads
         refframes[len - age], so the frames older than the largest age on the map are dead; dropping
-        them from the front leaves len - age pointing at the same frames.  The current frame always
-        stays (the next increment_age needs its pose and camera)."""
-        n = len(self._images)
-        counts = device.age_usage(self.age, n).cpu().numpy()   # ages 0..n, then older (impossible)
+        them from the front leaves len - age pointing at the same frames.  `counts` = pixels per age
+        for the map that went with a ring of n frames (frames appended since then are newer and stay).
+        The newest frame always stays (the next increment_age needs its pose and camera)."""
         used = np.nonzero(counts)[0]
         oldest = int(used.max()) if used.size else 0
-        # at the next track() the ages have grown by one and the list by one: frame index
-        # (n + 1) - (oldest + 1) = n - oldest is the oldest one still read
+        # at the next update the ages have grown by one and the ring by one: frame index
+        # (n + 1) - 1 - (oldest + 1) = n - 1 - oldest is the oldest one still read
         keep_from = max(0, min(n - 1 - oldest, n - 1))
         if keep_from > 0:
             del self._images[:keep_from], self._cams[:keep_from], self._poses[:keep_from]

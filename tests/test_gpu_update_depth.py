@@ -385,20 +385,24 @@ def test_smallest_accepted_workspace_gives_the_same_maps(monkeypatch):
     from tadataka_b200 import _lib, device
     b = scene.stack_keyframes([scene.make_keyframe(2600 + i, R=2, H=96, W=128, cam=scene.CAM_VGA / 5)
                                for i in range(5)])
-    want = _gpu(b, hist=True)
-    P, H, W = b["key_img"].shape
-    small = _lib.update_depth_workspace_bytes_min(P, 2, H, W)
-    assert 0 < small < _lib.update_depth_workspace_bytes(P, 2, H, W)
-    device._workspaces.clear()
-    monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small)
-    got = _gpu(b, hist=True)
-    for x, y in zip(want, got):
-        assert np.array_equal(x, y, equal_nan=True)
-    device._workspaces.clear()
-    monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small - 1)
-    with pytest.raises(_lib.TdkError, match="workspace"):
-        _gpu(b)
-    device._workspaces.clear()
+    try:
+        _lib.set_kernel_plan(2)   # the automatic choice would take the two-kernel plan at this size
+        want = _gpu(b, hist=True)
+        P, H, W = b["key_img"].shape
+        small = _lib.update_depth_workspace_bytes_min(P, 2, H, W)
+        assert 0 < small < _lib.update_depth_workspace_bytes(P, 2, H, W)
+        device._workspaces.clear()
+        monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small)
+        got = _gpu(b, hist=True)
+        for x, y in zip(want, got):
+            assert np.array_equal(x, y, equal_nan=True)
+        device._workspaces.clear()
+        monkeypatch.setattr(_lib, "update_depth_workspace_bytes", lambda *a: small - 1)
+        with pytest.raises(_lib.TdkError, match="workspace"):
+            _gpu(b)
+    finally:
+        device._workspaces.clear()
+        _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
 
 
 @pytest.mark.parametrize("min_gradient", [0.0, -1.0, 1e-200, 1e-3, 0.05, 0.2, 0.7, 1.5, 1e200, float("inf"),
