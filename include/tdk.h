@@ -220,6 +220,17 @@ int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1,
                       double uncertaintity_bias, double *depth1, double *variance1,
                       void *workspace, size_t workspace_bytes, void *stream);
 
+/* increment_age and propagate in one pass over the same warp, as the reference's loop calls them
+ * back to back with the same (T10, cameras, depth0) (examples/semi_dense_vo.py:185-194): age1 is what
+ * tdk_increment_age_dev returns, depth1 / variance1 what tdk_propagate_dev returns.  Same workspace
+ * as tdk_propagate_dev. */
+int tdk_propagate_age_dev(const double *T10, const double *cam0, const double *cam1,
+                          const double *depth0, const double *variance0, const uint64_t *age0,
+                          int64_t P, int64_t H, int64_t W, double default_depth,
+                          double default_variance, double uncertaintity_bias, double *depth1,
+                          double *variance1, uint64_t *age1, void *workspace, size_t workspace_bytes,
+                          void *stream);
+
 /* ------------------------------------------------------------------ helpers on the drop-in surface
  * rust_bindings.warp.warp_vecs        (src/py/warp.rs:53-67   -> src/warp.rs:31-50)
  * rust_bindings.interpolation.interpolation (src/py/interpolation.rs:6-16 -> src/interpolation.rs:57-73)

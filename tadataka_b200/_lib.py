@@ -59,6 +59,8 @@ increment_age_dev = _sig("tdk_increment_age_dev", C.c_int, P, P, P, P, P, I64, I
 propagate_workspace_bytes = _sig("tdk_propagate_workspace_bytes", SZ, I64, I64, I64)
 propagate_dev = _sig("tdk_propagate_dev", C.c_int, P, P, P, P, P, I64, I64, I64, D, D, D, P, P, P,
                      SZ, P)
+propagate_age_dev = _sig("tdk_propagate_age_dev", C.c_int, P, P, P, P, P, P, I64, I64, I64, D, D, D, P, P, P, P,
+                         SZ, P)
 warp_vecs_dev = _sig("tdk_warp_vecs_dev", C.c_int, P, P, P, I64, P, P, P)
 interpolate_dev = _sig("tdk_interpolate_dev", C.c_int, P, I64, I64, P, I64, P, P, P)
 project_vecs_dev = _sig("tdk_project_vecs_dev", C.c_int, P, I64, P, P)
@@ -86,7 +88,7 @@ EXPORTS = [
     "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",
     "tdk_propagate_dev", "tdk_warp_vecs_dev", "tdk_interpolate_dev", "tdk_project_vecs_dev",
     "tdk_inv_project_vecs_dev", "tdk_transform_dev", "tdk_calc_depth0_dev",
-    "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev",
+    "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev", "tdk_propagate_age_dev",
     "tdk_image_gradient_dev", "tdk_dvo_normal_equations_dev", "tdk_dvo_student_t_dev",
     "tdk_dvo_photometric_error_dev",
 ]

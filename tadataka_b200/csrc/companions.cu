@@ -170,19 +170,22 @@ __global__ void __launch_bounds__(TPB) age_gather_kernel(const uint64_t *__restr
     age1[(size_t)p * hw + t] = w ? age0[(size_t)p * hw + (w - 1u)] + 1ull : 0ull;
 }
 
-// --------------------------------------------------------------------------------- propagate
-// propagation.rs:48-92.  The reference folds colliding sources into a HashMap in raster order;
-// the fold is order dependent (gated fusion, nearer-depth-wins), so the GPU builds, per target,
-// the list of its sources (count -> exclusive scan -> fill), sorts each list by source index and
-// replays the same fold sequentially.
-__global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restrict__ T10,
-                                                         const double *__restrict__ cam0,
-                                                         const double *__restrict__ cam1,
-                                                         const double *__restrict__ depth0,
-                                                         const double *__restrict__ variance0, double bias,
-                                                         int H, int W, int *__restrict__ tgt,
-                                                         unsigned int *__restrict__ cnt, double *__restrict__ src_d1,
-                                                         double *__restrict__ src_v1)
+// ---- propagate (propagation.rs:9-92, stat.rs:5-26) ---------------------------------------------
+// The reference folds the sources of every target pixel in raster order of the SOURCE, and the fold
+// is order dependent (gated fusion, nearer-depth-wins).  Here every source pushes itself onto a
+// linked list at its target (one atomicExch on the target's head word); prop_fold_kernel walks the
+// list of its target, puts the sources in raster order -- up to four in registers through a sorting
+// network, which covers every target of an ordinary camera motion; longer lists in a scratch
+// segment, insertion or heap sort -- and replays the reference's fold.  Two kernels and one memset
+// per call, linear in the number of sources whatever the warp does.
+__global__ void __launch_bounds__(TPB) prop_scatter_kernel(const double *__restrict__ T10,
+                                                           const double *__restrict__ cam0,
+                                                           const double *__restrict__ cam1,
+                                                           const double *__restrict__ depth0,
+                                                           const double *__restrict__ variance0, double bias,
+                                                           int H, int W, unsigned int *__restrict__ head,
+                                                           unsigned int *__restrict__ next,
+                                                           double *__restrict__ src_d1, double *__restrict__ src_v1)
 {
     __shared__ double s_qx[RT_W], s_qy[RT_H];
     const int p = blockIdx.z;
@@ -191,129 +194,43 @@ __global__ void __launch_bounds__(TPB) prop_count_kernel(const double *__restric
     int x, y;
     double qx, qy, d1;
     if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
-    const size_t s = (size_t)p * hw + (size_t)y * W + x;
+    const unsigned int src = (unsigned int)(y * W + x);
+    const size_t s = (size_t)p * hw + src;
     const double d0 = depth0[s];
     const int t = warp_target_n(c, qx, qy, d0, H, W, d1);
-    tgt[s] = t;
     if (t < 0) return;
-    atomicAdd(cnt + (size_t)p * hw + t, 1u);
     // what this source carries to its target: propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
     const double ratio = tdk::inv(d1) / tdk::inv(d0);
     const double r2 = ratio * ratio;
     src_d1[s] = d1;
     src_v1[s] = (r2 * r2) * variance0[s] + bias;
+    next[s] = atomicExch(head + (size_t)p * hw + t, src + 1u);   // 0 terminates a list
 }
 
-// exclusive scan of n u32 values, 1024 per block: (a) block sums, (b) scan of the sums by one
-// block, (c) block-local scan + offset.  out has n+1 entries; out[n] = total.
-constexpr int SCAN_ITEMS = 4;
-constexpr int SCAN_TILE = TPB * SCAN_ITEMS;
-
-__device__ __forceinline__ unsigned int block_exclusive_scan(unsigned int v, unsigned int *s_warp,
-                                                             unsigned int &total)
+// handle_collision(a = new, b = stored), propagation.rs:21-46 ; stat.rs:5-26 ; fusion.rs:3-11
+__device__ __forceinline__ void fold_step(double d1a, double v1a, double &acc_d, double &acc_v)
 {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    unsigned int incl = v;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
-        if (lane >= off) incl += o;
+    const double ia = tdk::inv(d1a), ib = tdk::inv(acc_d);
+    const double ds = (ia - ib) * (ia - ib);
+    const double fs = TDK_STAT_FACTOR * TDK_STAT_FACTOR;
+    if (ds <= fs * v1a && ds <= fs * acc_v) {
+        const double v = v1a + acc_v;
+        const double mu = (ia * acc_v + ib * v1a) / v;
+        acc_d = tdk::inv(mu);
+        acc_v = (v1a * acc_v) / v;
+    } else if (d1a < acc_d) {
+        acc_d = d1a;
+        acc_v = v1a;
     }
-    if (lane == 31) s_warp[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        unsigned int w = lane < (int)(blockDim.x >> 5) ? s_warp[lane] : 0u;
-        unsigned int wi = w;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const unsigned int o = __shfl_up_sync(0xffffffffu, wi, off);
-            if (lane >= off) wi += o;
-        }
-        s_warp[lane] = wi - w;            // exclusive warp offsets
-        if (lane == 31) s_warp[32] = wi;  // block total
-    }
-    __syncthreads();
-    total = s_warp[32];
-    const unsigned int r = incl - v + s_warp[wid];
-    __syncthreads();
-    return r;
-}
-
-__global__ void __launch_bounds__(TPB) scan_sums_kernel(const unsigned int *__restrict__ in, size_t n,
-                                                        unsigned int *__restrict__ bsum)
-{
-    __shared__ unsigned int s_warp[33];
-    const size_t base = (size_t)blockIdx.x * SCAN_TILE;
-    unsigned int v = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        const size_t i = base + (size_t)k * TPB + threadIdx.x;
-        if (i < n) v += in[i];
-    }
-    unsigned int total;
-    block_exclusive_scan(v, s_warp, total);
-    if (threadIdx.x == 0) bsum[blockIdx.x] = total;
-}
-
-__global__ void __launch_bounds__(1024) scan_bsum_kernel(unsigned int *__restrict__ bsum, size_t m,
-                                                         unsigned int *__restrict__ total_out)
-{
-    __shared__ unsigned int s_warp[33];
-    unsigned int carry = 0;
-    for (size_t base = 0; base < m; base += 1024) {
-        const size_t i = base + threadIdx.x;
-        const unsigned int v = i < m ? bsum[i] : 0u;
-        unsigned int total;
-        const unsigned int ex = block_exclusive_scan(v, s_warp, total);
-        if (i < m) bsum[i] = carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0) *total_out = carry;
-}
-
-__global__ void __launch_bounds__(TPB) scan_apply_kernel(const unsigned int *__restrict__ in, size_t n,
-                                                         const unsigned int *__restrict__ bsum,
-                                                         unsigned int *__restrict__ out)
-{
-    __shared__ unsigned int s_warp[33];
-    const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
-    unsigned int v[SCAN_ITEMS], sum = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        v[k] = base + k < n ? in[base + k] : 0u;
-        sum += v[k];
-    }
-    unsigned int total;
-    unsigned int run = block_exclusive_scan(sum, s_warp, total) + bsum[blockIdx.x];
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        if (base + k < n) out[base + k] = run;
-        run += v[k];
-    }
-}
-
-__global__ void __launch_bounds__(TPB) prop_fill_kernel(const int *__restrict__ tgt,
-                                                        unsigned int *__restrict__ cnt,
-                                                        const unsigned int *__restrict__ off, int hw,
-                                                        unsigned int *__restrict__ list)
-{
-    const int p = blockIdx.y;
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= hw) return;
-    const int t = tgt[(size_t)p * hw + s];
-    if (t < 0) return;
-    const size_t g = (size_t)p * hw + t;
-    const unsigned int slot = atomicSub(cnt + g, 1u) - 1u;
-    list[off[g] + slot] = (unsigned int)s;
 }
 
 __device__ __forceinline__ void sift_down(unsigned int *a, unsigned int start, unsigned int end)
 {
     unsigned int root = start;
-    while (2u * root + 1u <= end) {
-        unsigned int child = 2u * root + 1u, sw = root;
+    while (2 * root + 1 <= end) {
+        unsigned int child = 2 * root + 1, sw = root;
         if (a[sw] < a[child]) sw = child;
-        if (child + 1u <= end && a[sw] < a[child + 1u]) sw = child + 1u;
+        if (child + 1 <= end && a[sw] < a[child + 1]) sw = child + 1;
         if (sw == root) return;
         const unsigned int tmp = a[root];
         a[root] = a[sw];
@@ -324,29 +241,63 @@ __device__ __forceinline__ void sift_down(unsigned int *a, unsigned int start, u
 
 __global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict__ src_d1,
                                                         const double *__restrict__ src_v1, int hw,
-                                                        const unsigned int *__restrict__ off,
-                                                        unsigned int *__restrict__ list, double def_d,
+                                                        const unsigned int *__restrict__ head,
+                                                        const unsigned int *__restrict__ next,
+                                                        unsigned int *__restrict__ list,
+                                                        unsigned int *__restrict__ list_cursor, double def_d,
                                                         double def_v, double *__restrict__ depth1,
-                                                        double *__restrict__ variance1)
+                                                        double *__restrict__ variance1,
+                                                        const uint64_t *__restrict__ age0,
+                                                        uint64_t *__restrict__ age1)
 {
     const int p = blockIdx.y;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= hw) return;
     const size_t g = (size_t)p * hw + t;
-    const unsigned int b = off[g], k = off[g + 1] - b;
-    if (k == 0) {
+    const unsigned int *__restrict__ nx = next + (size_t)p * hw;
+    const double *__restrict__ sd = src_d1 + (size_t)p * hw, *__restrict__ sv = src_v1 + (size_t)p * hw;
+    const unsigned int h = head[g];
+    if (h == 0) {
         depth1[g] = def_d;
         variance1[g] = def_v;
+        if (age1) age1[g] = 0ull;
         return;
     }
-    unsigned int *seg = list + b;
-    if (k > 1) {
-        if (k <= 16) {   // insertion sort: the common case is 2..4 sources per target
+    // the first four sources of the list, 0xffffffff where it is shorter
+    unsigned int a = h - 1u, b = 0xffffffffu, c = 0xffffffffu, d = 0xffffffffu, more = 0u;
+    unsigned int link = nx[a];
+    if (link) { b = link - 1u; link = nx[b]; }
+    if (link) { c = link - 1u; link = nx[c]; }
+    if (link) { d = link - 1u; more = nx[d]; }
+    double acc_d, acc_v;
+    unsigned int last;
+    if (more == 0u) {
+        unsigned int lo, hi;
+        lo = min(a, b); hi = max(a, b); a = lo; b = hi;
+        lo = min(c, d); hi = max(c, d); c = lo; d = hi;
+        lo = min(a, c); hi = max(a, c); a = lo; c = hi;
+        lo = min(b, d); hi = max(b, d); b = lo; d = hi;
+        lo = min(b, c); hi = max(b, c); b = lo; c = hi;
+        acc_d = sd[a]; acc_v = sv[a];
+        if (b != 0xffffffffu) fold_step(sd[b], sv[b], acc_d, acc_v);
+        if (c != 0xffffffffu) fold_step(sd[c], sv[c], acc_d, acc_v);
+        if (d != 0xffffffffu) fold_step(sd[d], sv[d], acc_d, acc_v);
+        last = d != 0xffffffffu ? d : c != 0xffffffffu ? c : b != 0xffffffffu ? b : a;
+    } else {
+        // longer list: copy it into a segment of the scratch list (the lists of different targets are
+        // disjoint, so the segments handed out per frame fit hw), sort, fold
+        unsigned int k = 4;
+        for (unsigned int l2 = more; l2; l2 = nx[l2 - 1u]) k++;
+        unsigned int *seg = list + (size_t)p * hw + atomicAdd(list_cursor + p, k);
+        seg[0] = a; seg[1] = b; seg[2] = c; seg[3] = d;
+        unsigned int j = 4;
+        for (unsigned int l2 = more; l2; l2 = nx[l2 - 1u]) seg[j++] = l2 - 1u;
+        if (k <= 16) {   // insertion sort
             for (unsigned int i = 1; i < k; i++) {
                 const unsigned int key = seg[i];
-                unsigned int j = i;
-                while (j > 0 && seg[j - 1] > key) { seg[j] = seg[j - 1]; j--; }
-                seg[j] = key;
+                unsigned int jj = i;
+                while (jj > 0 && seg[jj - 1] > key) { seg[jj] = seg[jj - 1]; jj--; }
+                seg[jj] = key;
             }
         } else {         // heap sort keeps degenerate many-to-one warps O(k log k)
             for (int start = (int)(k - 2) / 2; start >= 0; start--) sift_down(seg, (unsigned int)start, k - 1);
@@ -357,46 +308,33 @@ __global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict
                 sift_down(seg, 0, end - 1);
             }
         }
-    }
-    double acc_d = 0., acc_v = 0.;
-    for (unsigned int i = 0; i < k; i++) {
-        const unsigned int s = seg[i];
-        const double d1a = src_d1[(size_t)p * hw + s], v1a = src_v1[(size_t)p * hw + s];
-        if (i == 0) { acc_d = d1a; acc_v = v1a; continue; }
-        // handle_collision(a = new, b = stored), propagation.rs:21-46 ; stat.rs:5-26 ; fusion.rs:3-11
-        const double ia = tdk::inv(d1a), ib = tdk::inv(acc_d);
-        const double ds = (ia - ib) * (ia - ib);
-        const double fs = TDK_STAT_FACTOR * TDK_STAT_FACTOR;
-        if (ds <= fs * v1a && ds <= fs * acc_v) {
-            const double v = v1a + acc_v;
-            const double mu = (ia * acc_v + ib * v1a) / v;
-            acc_d = tdk::inv(mu);
-            acc_v = (v1a * acc_v) / v;
-        } else if (d1a < acc_d) {
-            acc_d = d1a;
-            acc_v = v1a;
-        }
+        acc_d = sd[seg[0]]; acc_v = sv[seg[0]];
+        for (unsigned int i = 1; i < k; i++) fold_step(sd[seg[i]], sv[seg[i]], acc_d, acc_v);
+        last = seg[k - 1];
     }
     depth1[g] = acc_d;
     variance1[g] = acc_v;
+    // age.rs:6-32 through the same warp: the last raster writer of a target is its largest source
+    if (age1) age1[g] = age0[(size_t)p * hw + last] + 1ull;
 }
 
 size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 
 struct PropLayout {
-    size_t tgt, cnt, off, list, bsum, src_d1, src_v1, total;
+    size_t head, list_cursor, clear_bytes, next, list, src_d1, src_v1, total;
 };
 PropLayout prop_layout(int64_t P, int64_t H, int64_t W)
 {
     const size_t n = (size_t)P * H * W;
-    const size_t m = (n + SCAN_TILE - 1) / SCAN_TILE;
     PropLayout l;
     size_t o = 0;
-    l.tgt = o; o = up256(o + n * 4);
-    l.cnt = o; o = up256(o + n * 4);
-    l.off = o; o = up256(o + (n + 1) * 4);
+    // cleared by one memset per call: the list heads and the per-frame cursors of the scratch list
+    l.head = o; o = o + n * 4;
+    l.list_cursor = o; o = o + (size_t)P * 4;
+    l.clear_bytes = o;
+    o = up256(o);
+    l.next = o; o = up256(o + n * 4);
     l.list = o; o = up256(o + n * 4);
-    l.bsum = o; o = up256(o + (m + 1) * 4);
     l.src_d1 = o; o = up256(o + n * 8);
     l.src_v1 = o; o = up256(o + n * 8);
     l.total = o;
@@ -539,49 +477,62 @@ size_t tdk_propagate_workspace_bytes(int64_t P, int64_t H, int64_t W)
     return prop_layout(P, H, W).total;
 }
 
+static int propagate_launch(const char *who, const double *T10, const double *cam0, const double *cam1,
+                            const double *depth0, const double *variance0, const uint64_t *age0, int64_t P,
+                            int64_t H, int64_t W, double default_depth, double default_variance,
+                            double uncertaintity_bias, double *depth1, double *variance1, uint64_t *age1,
+                            void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || !workspace ||
+        ((age0 == nullptr) != (age1 == nullptr))) {
+        tdk_set_error("%s: null pointer argument", who);
+        return TDK_ERR_INVALID;
+    }
+    int rc = check_frames(who, P, H, W);
+    if (rc != TDK_OK) return rc;
+    const PropLayout l = prop_layout(P, H, W);
+    if (workspace_bytes < l.total) {
+        tdk_set_error("%s: workspace %zu < required %zu", who, workspace_bytes, l.total);
+        return TDK_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    char *ws = (char *)workspace;
+    unsigned int *head = (unsigned int *)(ws + l.head), *next = (unsigned int *)(ws + l.next);
+    unsigned int *list_cursor = (unsigned int *)(ws + l.list_cursor), *list = (unsigned int *)(ws + l.list);
+    double *src_d1 = (double *)(ws + l.src_d1), *src_v1 = (double *)(ws + l.src_v1);
+    const int hw = (int)(H * W);
+    TDK_CUDA(cudaMemsetAsync(ws, 0, l.clear_bytes, st));
+    dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
+    dim3 tgrid((unsigned)((W + RT_W - 1) / RT_W), (unsigned)((H + RT_H - 1) / RT_H), (unsigned)P);
+    prop_scatter_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, variance0, uncertaintity_bias, (int)H,
+                                               (int)W, head, next, src_d1, src_v1);
+    TDK_CUDA(cudaGetLastError());
+    prop_fold_kernel<<<grid, TPB, 0, st>>>(src_d1, src_v1, hw, head, next, list, list_cursor, default_depth,
+                                           default_variance, depth1, variance1, age0, age1);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
 int tdk_propagate_dev(const double *T10, const double *cam0, const double *cam1, const double *depth0,
                       const double *variance0, int64_t P, int64_t H, int64_t W, double default_depth,
                       double default_variance, double uncertaintity_bias, double *depth1, double *variance1,
                       void *workspace, size_t workspace_bytes, void *stream)
 {
-    if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || !workspace) {
-        tdk_set_error("tdk_propagate_dev: null pointer argument");
-        return TDK_ERR_INVALID;
-    }
-    int rc = check_frames("tdk_propagate_dev", P, H, W);
-    if (rc != TDK_OK) return rc;
-    const PropLayout l = prop_layout(P, H, W);
-    if (workspace_bytes < l.total) {
-        tdk_set_error("tdk_propagate_dev: workspace %zu < required %zu", workspace_bytes, l.total);
-        return TDK_ERR_WORKSPACE;
-    }
-    cudaStream_t st = (cudaStream_t)stream;
-    char *ws = (char *)workspace;
-    int *tgt = (int *)(ws + l.tgt);
-    unsigned int *cnt = (unsigned int *)(ws + l.cnt), *off = (unsigned int *)(ws + l.off);
-    unsigned int *list = (unsigned int *)(ws + l.list), *bsum = (unsigned int *)(ws + l.bsum);
-    const int hw = (int)(H * W);
-    const size_t n = (size_t)P * hw;
-    const size_t m = (n + SCAN_TILE - 1) / SCAN_TILE;
-    TDK_CUDA(cudaMemsetAsync(cnt, 0, n * 4, st));
-    dim3 grid((unsigned)((hw + TPB - 1) / TPB), (unsigned)P);
-    dim3 tgrid((unsigned)((W + RT_W - 1) / RT_W), (unsigned)((H + RT_H - 1) / RT_H), (unsigned)P);
-    double *src_d1 = (double *)(ws + l.src_d1), *src_v1 = (double *)(ws + l.src_v1);
-    prop_count_kernel<<<tgrid, TPB, 0, st>>>(T10, cam0, cam1, depth0, variance0, uncertaintity_bias, (int)H, (int)W,
-                                             tgt, cnt, src_d1, src_v1);
-    TDK_CUDA(cudaGetLastError());
-    scan_sums_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum);
-    TDK_CUDA(cudaGetLastError());
-    scan_bsum_kernel<<<1, 1024, 0, st>>>(bsum, m, off + n);
-    TDK_CUDA(cudaGetLastError());
-    scan_apply_kernel<<<(unsigned)m, TPB, 0, st>>>(cnt, n, bsum, off);
-    TDK_CUDA(cudaGetLastError());
-    prop_fill_kernel<<<grid, TPB, 0, st>>>(tgt, cnt, off, hw, list);
-    TDK_CUDA(cudaGetLastError());
-    prop_fold_kernel<<<grid, TPB, 0, st>>>(src_d1, src_v1, hw, off, list, default_depth, default_variance, depth1,
-                                           variance1);
-    TDK_CUDA(cudaGetLastError());
-    return TDK_OK;
+    return propagate_launch("tdk_propagate_dev", T10, cam0, cam1, depth0, variance0, nullptr, P, H, W, default_depth,
+                            default_variance, uncertaintity_bias, depth1, variance1, nullptr, workspace,
+                            workspace_bytes, stream);
+}
+
+int tdk_propagate_age_dev(const double *T10, const double *cam0, const double *cam1, const double *depth0,
+                          const double *variance0, const uint64_t *age0, int64_t P, int64_t H, int64_t W,
+                          double default_depth, double default_variance, double uncertaintity_bias,
+                          double *depth1, double *variance1, uint64_t *age1, void *workspace,
+                          size_t workspace_bytes, void *stream)
+{
+    if (!age0 || !age1) { tdk_set_error("tdk_propagate_age_dev: null pointer argument"); return TDK_ERR_INVALID; }
+    return propagate_launch("tdk_propagate_age_dev", T10, cam0, cam1, depth0, variance0, age0, P, H, W,
+                            default_depth, default_variance, uncertaintity_bias, depth1, variance1, age1, workspace,
+                            workspace_bytes, stream);
 }
 
 }  // extern "C"

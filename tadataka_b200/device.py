@@ -249,6 +249,34 @@ def propagate(T10, cam0, cam1, depth0, variance0, default_depth, default_varianc
     return d1, v1
 
 
+def propagate_with_age(T10, cam0, cam1, depth0, variance0, age0, default_depth, default_variance,
+                       uncertaintity_bias):
+    """increment_age + propagate through one warp of the map (tdk_propagate_age_dev): what the
+    reference's loop computes with two calls on the same (T10, cameras, depth0)
+    (examples/semi_dense_vo.py:185-194).  -> (depth1, variance1, age1)."""
+    _require_cuda()
+    d3 = _as3(depth0)
+    P, H, W = d3.shape
+    _chk(depth0, "depth0", _F64)
+    _chk(variance0, "variance0", _F64, depth0.shape)
+    _chk(age0, "age0", torch.uint64, depth0.shape)
+    _chk(cam0, "cam0", _F64)
+    _chk(cam1, "cam1", _F64)
+    _chk(T10, "T10", _F64)
+    if cam0.numel() != 4 * P or cam1.numel() != 4 * P or T10.numel() != 16 * P:
+        raise ValueError("cam0/cam1/T10 do not match the number of frames")
+    dev = depth0.device
+    with torch.cuda.device(dev):
+        d1, v1 = torch.empty_like(depth0), torch.empty_like(depth0)
+        a1 = torch.empty_like(age0)
+        ws = workspace(_lib.propagate_workspace_bytes(P, H, W), dev, "propagate")
+        _lib.check(_lib.propagate_age_dev(_ptr(T10), _ptr(cam0), _ptr(cam1), _ptr(depth0), _ptr(variance0),
+                                          _ptr(age0), P, H, W, float(default_depth), float(default_variance),
+                                          float(uncertaintity_bias), _ptr(d1), _ptr(v1), _ptr(a1), _ptr(ws),
+                                          ws.numel(), _stream()))
+    return d1, v1, a1
+
+
 # ------------------------------------------------------------------ vectorised helpers
 def warp_vecs(T10, xs0, depths0):
     _require_cuda()

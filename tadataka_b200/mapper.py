@@ -83,9 +83,10 @@ class SemiDenseMapper:
         g_cams = g_small[40:40 + 4 * R].view(R, 4)
         g_poses = g_small[40 + 4 * R:40 + 20 * R].view(R, 4, 4)
         g_img = _upload(image)
-        age1 = device.increment_age(self.age, g_cam0, g_cam1, g_T10, self.depth)
-        depth1, var1 = device.propagate(g_T10, g_cam0, g_cam1, self.depth, self.variance,
-                                        self.default_depth, self.default_variance, self.bias)
+        # increment_age + propagate (semi_dense_vo.py:185-194) through one warp of the map
+        depth1, var1, age1 = device.propagate_with_age(g_T10, g_cam0, g_cam1, self.depth, self.variance,
+                                                       self.age, self.default_depth, self.default_variance,
+                                                       self.bias)
         d, v, f = device.update_depth_frames(g_img, g_cam1, g_Tw1, self._images, g_cams, g_poses,
                                              age1, depth1, var1, self.params, fuse=self.fuse)
         if self.smooth:

@@ -148,6 +148,9 @@ def test_propagate_and_age_batched():
         od, ov = ora.propagate(T10[i], cam, cam, d0[i], v0[i], 250.0, 10.0, 1e-5)
         assert np.array_equal(d1[i].cpu().numpy(), od) and np.array_equal(v1[i].cpu().numpy(), ov)
         assert np.array_equal(a1[i].cpu().numpy(), ora.increment_age(a0[i], cam, cam, T10[i], d0[i]))
+    # the fused entry point (one warp of the map for both) gives the same three maps
+    fd, fv, fa = device.propagate_with_age(cu(T10), cu(cams), cu(cams), cu(d0), cu(v0), cu(a0), 250.0, 10.0, 1e-5)
+    assert torch.equal(fd, d1) and torch.equal(fv, v1) and torch.equal(fa, a1)
 
 
 # ------------------------------------------------------------------ helper surface

@@ -54,6 +54,8 @@ rows = [
     ("regularize (32 B/px)", 32, lambda: device.regularize(depth, var, flag)),
     ("increment_age (24 B/px)", 24, lambda: device.increment_age(age, cams, cams, T10, depth)),
     ("propagate (32 B/px)", 32, lambda: device.propagate(T10, cams, cams, depth, var, 200.0, 100.0, 1e-6)),
+    ("propagate + increment_age, one pass (48 B/px)", 48,
+     lambda: device.propagate_with_age(T10, cams, cams, depth, var, age, 200.0, 100.0, 1e-6)),
 ]
 print(f"{P} x {W}x{H} frames, HBM peak {PEAK} GB/s")
 for name, bpp, fn in rows:
