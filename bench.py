@@ -247,6 +247,10 @@ def run_b200(args, rank, world, local_rank):
         except Exception:
             pass
     if world > 1:
+        # NCCL_DEBUG=VERSION (set on some boxes) makes NCCL print a banner on stdout, where the bench
+        # contract wants exactly one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     if args.plan >= 0:
         _lib.check(_lib.set_kernel_plan(args.plan))
