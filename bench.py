@@ -247,11 +247,19 @@ def run_b200(args, rank, world, local_rank):
         except Exception:
             pass
     if world > 1:
-        # NCCL_DEBUG=VERSION (set on some boxes) makes NCCL print a banner on stdout, where the bench
-        # contract wants exactly one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints a version banner on stdout when the communicator is created; the bench contract
+        # wants exactly one JSON line there, so stdout points at stderr while NCCL starts up
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            C.CDLL(None).fflush(None)
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     if args.plan >= 0:
         _lib.check(_lib.set_kernel_plan(args.plan))
 
