@@ -21,6 +21,7 @@ ap.add_argument("--iters", type=int, default=20)
 ap.add_argument("--plans", default="0,1")
 ap.add_argument("--c4", action="store_true", help="720p TUM-scale pairs instead of C2")
 ap.add_argument("--no-parity", action="store_true")
+ap.add_argument("--smooth", action="store_true", help="prior variance constant per 32x32 block, prior depth = ground truth with a smooth 3 %% bias (what a propagated map looks like) instead of per-pixel noise")
 args = ap.parse_args()
 
 if args.c4:
@@ -29,6 +30,15 @@ if args.c4:
 else:
     b = bench.make_workload(0, args.keyframes, args.distinct)
 P, H, W = b["key_img"].shape
+if args.smooth:
+    rng = np.random.default_rng(11)
+    by, bx = (H + 31) // 32, (W + 31) // 32
+    blocks = 10.0 ** rng.uniform(-3.0, 0.0, size=(P, by, bx))
+    b["prior_variance"] = np.ascontiguousarray(np.kron(blocks, np.ones((32, 32)))[:, :H, :W])
+    yy, xx = np.mgrid[0:H, 0:W]
+    bias = 1.0 + 0.03 * np.sin(xx / 97.0) * np.cos(yy / 71.0)
+    lo, hi = b["params"][0], b["params"][1]
+    b["prior_depth"] = np.ascontiguousarray(np.clip(b["gt_depth"] * bias, lo * 1.01, hi * 0.99))
 names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth", "prior_variance"]
 t = {k: torch.from_numpy(b[k]).cuda() for k in names}
 if not args.no_parity:
