@@ -42,20 +42,21 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
 // -------------------------------------------------------------------------------- regularize
 // regularization.rs:29-64 : sum over the zero-padded 3x3 (row-major) of id*iv / sum of iv where
 // flag == Success; no Success cell -> the input depth is kept.
-// A CTA stages id*iv and iv of its 64x4 tile plus a one-pixel halo in shared memory (two
-// inversions per pixel instead of two per neighbour visit); cells the reference skips hold exact
-// zeros, which leave its left-to-right sums unchanged.
-constexpr int RT_W = 64, RT_H = 4;
+// A CTA stages id*iv and iv of its 64x16 tile plus a one-pixel halo in shared memory (two
+// inversions per pixel instead of two per neighbour visit; 18 rows read for 16 written); cells the
+// reference skips hold exact zeros, which leave its left-to-right sums unchanged.
+constexpr int RT_W = 64, RT_H = 4;      // source tiles of the forward-warp kernels below
+constexpr int REG_W = 64, REG_H = 16;   // regularize tile
 __global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restrict__ depth,
                                                          const double *__restrict__ variance,
                                                          const long long *__restrict__ flag, int P, int H,
                                                          int W, double *__restrict__ out)
 {
-    __shared__ double s_prod[RT_H + 2][RT_W + 2], s_iv[RT_H + 2][RT_W + 2];
-    const int x0 = blockIdx.x * RT_W, y0 = blockIdx.y * RT_H;
+    __shared__ double s_prod[REG_H + 2][REG_W + 2], s_iv[REG_H + 2][REG_W + 2];
+    const int x0 = blockIdx.x * REG_W, y0 = blockIdx.y * REG_H;
     const size_t base = (size_t)blockIdx.z * H * W;
-    for (int e = threadIdx.x; e < (RT_H + 2) * (RT_W + 2); e += TPB) {
-        const int hy = e / (RT_W + 2), hx = e - hy * (RT_W + 2);
+    for (int e = threadIdx.x; e < (REG_H + 2) * (REG_W + 2); e += TPB) {
+        const int hy = e / (REG_W + 2), hx = e - hy * (REG_W + 2);
         const int yy = y0 - 1 + hy, xx = x0 - 1 + hx;
         double prod = 0., iv = 0.;
         if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
@@ -70,20 +71,24 @@ __global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restric
         s_iv[hy][hx] = iv;
     }
     __syncthreads();
-    const int lx = threadIdx.x & (RT_W - 1), ly = threadIdx.x / RT_W;
-    const int x = x0 + lx, y = y0 + ly;
-    if (x >= W || y >= H) return;
-    double num = 0., den = 0.;
+    const int lx = threadIdx.x & (REG_W - 1);
+    const int x = x0 + lx;
+    if (x >= W) return;
+    for (int ly = threadIdx.x / REG_W; ly < REG_H; ly += TPB / REG_W) {
+        const int y = y0 + ly;
+        if (y >= H) break;
+        double num = 0., den = 0.;
 #pragma unroll
-    for (int dy = 0; dy < 3; dy++) {
+        for (int dy = 0; dy < 3; dy++) {
 #pragma unroll
-        for (int dx = 0; dx < 3; dx++) {
-            num = num + s_prod[ly + dy][lx + dx];
-            den = den + s_iv[ly + dy][lx + dx];
+            for (int dx = 0; dx < 3; dx++) {
+                num = num + s_prod[ly + dy][lx + dx];
+                den = den + s_iv[ly + dy][lx + dx];
+            }
         }
+        const size_t c = base + (size_t)y * W + x;
+        out[c] = den == 0. ? depth[c] : tdk::inv(num / den);
     }
-    const size_t c = base + (size_t)y * W + x;
-    out[c] = den == 0. ? depth[c] : tdk::inv(num / den);
 }
 
 // ------------------------------------------------------------------- forward warp of a pixel
@@ -410,7 +415,7 @@ int tdk_regularize_dev(const double *depth, const double *variance, const int64_
     }
     int rc = check_frames("tdk_regularize_dev", P, H, W);
     if (rc != TDK_OK) return rc;
-    dim3 grid((unsigned)((W + 63) / 64), (unsigned)((H + 3) / 4), (unsigned)P);
+    dim3 grid((unsigned)((W + REG_W - 1) / REG_W), (unsigned)((H + REG_H - 1) / REG_H), (unsigned)P);
     regularize_kernel<<<grid, TPB, 0, (cudaStream_t)stream>>>(depth, variance, (const long long *)flag, (int)P,
                                                               (int)H, (int)W, out_depth);
     TDK_CUDA(cudaGetLastError());
