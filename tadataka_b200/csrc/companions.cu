@@ -46,6 +46,10 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
 // inversions per pixel instead of two per neighbour visit; 18 rows read for 16 written); cells the
 // reference skips hold exact zeros, which leave its left-to-right sums unchanged.
 constexpr int RT_W = 64, RT_H = 4;      // source tiles of the forward-warp kernels below
+#ifndef TDK_SCATTER_MIN_CTAS
+#define TDK_SCATTER_MIN_CTAS 8   // these kernels wait on loads and atomics: 64 resident warps beat 32 (9.5 vs 11.3 us per frame)
+#endif
+constexpr int SCATTER_MIN_CTAS = TDK_SCATTER_MIN_CTAS;
 constexpr int REG_W = 64, REG_H = 16;   // regularize tile
 __global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restrict__ depth,
                                                          const double *__restrict__ variance,
@@ -146,7 +150,7 @@ __device__ __forceinline__ bool tile_source(const FrameConst &c, int H, int W, d
     return x < W && y < H;
 }
 
-__global__ void __launch_bounds__(TPB) age_scatter_kernel(const double *__restrict__ T10,
+__global__ void __launch_bounds__(TPB, SCATTER_MIN_CTAS) age_scatter_kernel(const double *__restrict__ T10,
                                                           const double *__restrict__ cam0,
                                                           const double *__restrict__ cam1,
                                                           const double *__restrict__ depth0, int H, int W,
@@ -183,7 +187,7 @@ __global__ void __launch_bounds__(TPB) age_gather_kernel(const uint64_t *__restr
 // network, which covers every target of an ordinary camera motion; longer lists in a scratch
 // segment, insertion or heap sort -- and replays the reference's fold.  Two kernels and one memset
 // per call, linear in the number of sources whatever the warp does.
-__global__ void __launch_bounds__(TPB) prop_scatter_kernel(const double *__restrict__ T10,
+__global__ void __launch_bounds__(TPB, SCATTER_MIN_CTAS) prop_scatter_kernel(const double *__restrict__ T10,
                                                            const double *__restrict__ cam0,
                                                            const double *__restrict__ cam1,
                                                            const double *__restrict__ depth0,
@@ -244,7 +248,10 @@ __device__ __forceinline__ void sift_down(unsigned int *a, unsigned int start, u
     }
 }
 
-__global__ void __launch_bounds__(TPB) prop_fold_kernel(const double *__restrict__ src_d1,
+#ifndef TDK_FOLD_MIN_CTAS
+#define TDK_FOLD_MIN_CTAS 8
+#endif
+__global__ void __launch_bounds__(TPB, TDK_FOLD_MIN_CTAS) prop_fold_kernel(const double *__restrict__ src_d1,
                                                         const double *__restrict__ src_v1, int hw,
                                                         const unsigned int *__restrict__ head,
                                                         const unsigned int *__restrict__ next,
