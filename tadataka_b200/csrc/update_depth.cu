@@ -25,7 +25,7 @@ constexpr int BLOCK = TILE_W * TILE_H;
 #define TDK_MIN_CTAS 4
 #endif
 #ifndef TDK_SIEVE_MIN_CTAS
-#define TDK_SIEVE_MIN_CTAS 6
+#define TDK_SIEVE_MIN_CTAS 8
 #endif
 constexpr int MIN_CTAS = TDK_MIN_CTAS;       // resident CTAs per SM the register allocation is tuned for
 constexpr int SIEVE_MIN_CTAS = TDK_SIEVE_MIN_CTAS;
