@@ -1256,8 +1256,10 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 if (p0 > 0)   // pair_setup_kernel cleared them for the first sub-batch
                     TDK_CUDA(cudaMemsetAsync(a.len_hist, 0, (size_t)l.sub * 2 * LEN_CLASSES * sizeof(unsigned int), stream));
                 const dim3 sgrid(qx, 1u, ns);
-                // 32 resident warps per SM at match_kernel's 64 registers
-                a.warp_budget = (int)((int64_t)sm_count * 32 / ns);
+                // 32 resident warps per SM at match_kernel's 64 registers.  Only launches of one or two
+                // keyframes leave warps idle; in a batch a sparse keyframe's spare warps belong to its
+                // neighbours, and whole-warp searches of short lines would cost throughput there.
+                a.warp_budget = ns <= 2 ? (int)((int64_t)sm_count * 32 / ns) : 0;
                 const unsigned mx = (unsigned)((a.warp_budget + BLOCK / 32 - 1) / (BLOCK / 32));
                 update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
                 update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
