@@ -1,11 +1,12 @@
 """Aggregate an ncu report's source page by CUDA source line and by kernel phase.
-    python tools/ncu_lines.py gpurun_out/prof.ncu-rep [top_n]"""
+    python tools/ncu_lines.py gpurun_out/prof.ncu-rep [top_n] [kernel-name-substring]"""
 import csv
 import subprocess
 import sys
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+only = sys.argv[3] if len(sys.argv) > 3 else None
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
@@ -18,7 +19,7 @@ def toi(s):
         return 0
 
 
-agg, cur, first_kernel, nk = {}, None, True, 0
+agg, cur, first_kernel, nk, skip = {}, None, True, 0, False
 stall_cols = {}
 for r in rows:
     if not r:
@@ -27,12 +28,13 @@ for r in rows:
         cur = r[1].split("/")[-1]
         continue
     if r[0] == "Function Name":
+        skip = only is not None and only not in r[1]
         continue
     if r[0] == "Line No":
         i_s, i_i, i_t = r.index("# Samples"), r.index("Instructions Executed"), r.index("Thread Instructions Executed")
         stall_cols = {n: i for i, n in enumerate(r) if n.startswith("stall_") and "Not Issued" not in n}
         continue
-    if r[0].isdigit():
+    if r[0].isdigit() and not skip:
         key = (cur, int(r[0]))
         a = agg.setdefault(key, [r[1], 0, 0, 0, {}])
         a[1] += toi(r[i_s]); a[2] += toi(r[i_i]); a[3] += toi(r[i_t])
