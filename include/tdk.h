@@ -262,6 +262,12 @@ int tdk_render_scene_dev(const double *planes, const double *tex, const double *
                          double z0, const double *T_wc, const double *cams, int64_t N, int64_t H,
                          int64_t W, double *image, double *depth, void *stream);
 
+/* Test hook with no counterpart in the reference (host arithmetic only, needs no GPU): the sieve
+ * evaluates `sqrt(s) < min_gradient` (semi_dense.rs:130-134) as `s < T`; this returns that T, the
+ * smallest double whose square root is not below min_gradient (0 for min_gradient <= 0, NaN for
+ * NaN). */
+double tdk_sqrt_threshold(double min_gradient);
+
 /* Test hook with no counterpart in the reference.  The kernels divide several numerators by one
  * denominator with nvcc's own division sequence, sharing the part that depends on the denominator
  * only (tdk_common.cuh, tdk::div2 / tdk::div5).  This runs n pseudo-random cases (seeded; ordinary

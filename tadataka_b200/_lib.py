@@ -69,6 +69,7 @@ transform_dev = _sig("tdk_transform_dev", C.c_int, P, P, I64, P, P)
 calc_depth0_dev = _sig("tdk_calc_depth0_dev", C.c_int, P, P, P, I64, P, P)
 age_usage_dev = _sig("tdk_age_usage_dev", C.c_int, P, I64, I64, I64, I64, P, P)
 render_scene_dev = _sig("tdk_render_scene_dev", C.c_int, P, P, P, I64, C.c_double, P, P, I64, I64, I64, P, P, P)
+sqrt_threshold = _sig("tdk_sqrt_threshold", C.c_double, C.c_double)
 selftest_shared_division_dev = _sig("tdk_selftest_shared_division_dev", C.c_int, I64, C.c_uint64, P, P)
 
 image_gradient_dev = _sig("tdk_image_gradient_dev", C.c_int, P, I64, I64, P, P, P)
@@ -88,7 +89,7 @@ EXPORTS = [
     "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",
     "tdk_propagate_dev", "tdk_warp_vecs_dev", "tdk_interpolate_dev", "tdk_project_vecs_dev",
     "tdk_inv_project_vecs_dev", "tdk_transform_dev", "tdk_calc_depth0_dev",
-    "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev", "tdk_propagate_age_dev",
+    "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev", "tdk_propagate_age_dev", "tdk_sqrt_threshold",
     "tdk_image_gradient_dev", "tdk_dvo_normal_equations_dev", "tdk_dvo_student_t_dev",
     "tdk_dvo_photometric_error_dev",
 ]

@@ -1328,6 +1328,9 @@ size_t tdk_update_depth_workspace_bytes_min(int64_t P, int64_t R, int64_t H, int
     return ws_layout(P, R, H, W, 1).total;
 }
 
+// test hook: the threshold the sieve compares the squared gradient norm with (host arithmetic only)
+double tdk_sqrt_threshold(double min_gradient) { return sqrt_threshold(min_gradient); }
+
 // tuning knob (not part of the reference surface): how update_depth is mapped onto kernels
 int tdk_set_kernel_plan(int plan)
 {

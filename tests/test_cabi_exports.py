@@ -119,3 +119,35 @@ def test_argument_errors_are_raised_before_any_cuda_call():
     assert (out_f == -9).all() and np.array_equal(out_d, d)
     with pytest.raises(ValueError, match="Age exceeds"):
         update_depth(frame, [], age, d, v, params)
+
+
+def test_square_root_threshold_is_exact():
+    """tdk_sqrt_threshold(m) must be the smallest double T with sqrt(T) >= m, so that the sieve's
+    `s < T` is the reference's `sqrt(s) < m` for every s (host arithmetic, no GPU needed)."""
+    import math
+    import numpy as np
+    from tadataka_b200 import _lib
+    rng = np.random.default_rng(5)
+    ms = list(10.0 ** rng.uniform(-300, 300, 300)) + list(rng.uniform(0.0, 2.0, 300))
+    ms += [0.2, 0.05, 1.0, 2.0 ** -537, 2.0 ** 511.5, 5e-324, 1.7976931348623157e308, 1e-162, 1.4e-162]
+    for m in ms:
+        T = _lib.sqrt_threshold(m)
+        assert math.sqrt(T) >= m, (m, T)
+        below = np.nextafter(T, 0.0)
+        assert T == 0.0 or math.sqrt(below) < m, (m, T)
+    assert _lib.sqrt_threshold(0.0) == 0.0 and _lib.sqrt_threshold(-3.0) == 0.0
+    assert math.isnan(_lib.sqrt_threshold(float("nan")))
+    assert _lib.sqrt_threshold(float("inf")) == float("inf")
+
+
+def test_update_depth_workspace_sizes():
+    from tadataka_b200 import _lib
+    H, W, R = 480, 640, 8
+    full = [_lib.update_depth_workspace_bytes(P, R, H, W) for P in (1, 2, 64, 65, 300)]
+    least = [_lib.update_depth_workspace_bytes_min(P, R, H, W) for P in (1, 2, 64, 65, 300)]
+    assert all(a >= b > 0 for a, b in zip(full, least)) and full[0] == least[0]
+    assert full == sorted(full) and least == sorted(least)
+    # beyond 64 keyframes only the per-keyframe queue grows (4 bytes per pixel and small constants)
+    per_kf = (full[4] - full[3]) / (300 - 65)
+    assert 4 * H * W <= per_kf < 5 * H * W
+    assert (full[2] - full[1]) / 62 > 137 * H * W
