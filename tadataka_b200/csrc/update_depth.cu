@@ -966,27 +966,36 @@ __device__ __forceinline__ void class_starts(const unsigned int *__restrict__ hi
     }
 }
 
+constexpr int ORDER_ITEMS = 4;   // queue slots per thread and round of order_kernel
+
 __global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs a)
 {
     __shared__ unsigned int s_start[LEN_CLASSES], s_cnt[LEN_CLASSES], s_off[LEN_CLASSES];
     const int tid = threadIdx.x;
     const int pl = blockIdx.z, p = pl + a.p0;
     const int total = (int)a.cand_count[p];
-    if ((int)blockIdx.x * BLOCK >= total) return;
-    const size_t ws_base = (size_t)pl * a.H * a.W;
+    constexpr int ROUND = BLOCK * ORDER_ITEMS;
+    if ((int)blockIdx.x * ROUND >= total) return;
+    const size_t ws_base = (size_t)pl * a.H * a.W;   // a multiple of 4 is not guaranteed: byte loads below
     class_starts(a.len_hist + pl * LEN_CLASSES, s_start, tid);
-    for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
+    for (int first = (int)blockIdx.x * ROUND; first < total; first += (int)gridDim.x * ROUND) {
         if (tid < LEN_CLASSES) s_cnt[tid] = 0;
         __syncthreads();
-        const int i = first + tid;
-        const int cls = i < total ? (int)a.len_class[ws_base + i] : 0;
-        unsigned int rank = 0;
-        if (cls) rank = atomicAdd(&s_cnt[cls], 1u);
+        int cls[ORDER_ITEMS];
+        unsigned int rank[ORDER_ITEMS];
+#pragma unroll
+        for (int k = 0; k < ORDER_ITEMS; k++) {
+            const int i = first + k * BLOCK + tid;
+            cls[k] = i < total ? (int)a.len_class[ws_base + i] : 0;
+            rank[k] = cls[k] ? atomicAdd(&s_cnt[cls[k]], 1u) : 0u;
+        }
         __syncthreads();
         if (tid < LEN_CLASSES && tid > 0 && s_cnt[tid])
             s_off[tid] = atomicAdd(&a.len_cursor[pl * LEN_CLASSES + tid], s_cnt[tid]);
         __syncthreads();
-        if (cls) a.order[ws_base + s_start[cls] + s_off[cls] + rank] = (unsigned int)i;
+#pragma unroll
+        for (int k = 0; k < ORDER_ITEMS; k++)
+            if (cls[k]) a.order[ws_base + s_start[cls[k]] + s_off[cls[k]] + rank[k]] = (unsigned int)(first + k * BLOCK + tid);
     }
 }
 
@@ -1263,7 +1272,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 const unsigned mx = (unsigned)((a.warp_budget + BLOCK / 32 - 1) / (BLOCK / 32));
                 update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
                 update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
-                update_depth_order_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
+                update_depth_order_kernel<<<dim3((qx + ORDER_ITEMS - 1) / ORDER_ITEMS, 1u, ns), BLOCK, 0, stream>>>(a);
                 update_depth_match_kernel<<<dim3(mx > qx ? mx : qx, 1u, ns), BLOCK, 0, stream>>>(a);
                 TDK_CUDA(cudaGetLastError());
             }
