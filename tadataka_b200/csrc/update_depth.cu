@@ -999,7 +999,11 @@ __global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs
     }
 }
 
-__global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kernel(const UpdArgs a)
+#ifndef TDK_MATCH_BLOCK
+#define TDK_MATCH_BLOCK 128   // four warps per CTA: finer-grained scheduling of the longest-first item order (18.1 vs 18.3 us per keyframe)
+#endif
+constexpr int MATCH_BLOCK = TDK_MATCH_BLOCK;
+__global__ void __launch_bounds__(MATCH_BLOCK, MATCH_MIN_CTAS * BLOCK / MATCH_BLOCK) update_depth_match_kernel(const UpdArgs a)
 {
     __shared__ unsigned int s_hist[10], s_start[LEN_CLASSES];
     const int tid = threadIdx.x, lane = tid & 31;
@@ -1024,7 +1028,7 @@ __global__ void __launch_bounds__(BLOCK, MATCH_MIN_CTAS) update_depth_match_kern
     const int nlong = (int)s_start[whole - 1];
     const int nitems = nlong + (nlive - nlong + 31) / 32;
     const TdkKeyConst key = a.keys[p];
-    const int warps = BLOCK / 32;
+    const int warps = MATCH_BLOCK / 32;
 
     for (int item = (int)blockIdx.x * warps + (tid >> 5); item < nitems; item += (int)gridDim.x * warps) {
         __syncwarp();   // `item` is warp-uniform: lanes that left the previous item early wait here
@@ -1269,11 +1273,12 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 // keyframes leave warps idle; in a batch a sparse keyframe's spare warps belong to its
                 // neighbours, and whole-warp searches of short lines would cost throughput there.
                 a.warp_budget = ns <= 2 ? (int)((int64_t)sm_count * 32 / ns) : 0;
-                const unsigned mx = (unsigned)((a.warp_budget + BLOCK / 32 - 1) / (BLOCK / 32));
+                const unsigned mx = (unsigned)((a.warp_budget + MATCH_BLOCK / 32 - 1) / (MATCH_BLOCK / 32));
+                const unsigned mq = qx * (BLOCK / MATCH_BLOCK);
                 update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
                 update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
                 update_depth_order_kernel<<<dim3((qx + ORDER_ITEMS - 1) / ORDER_ITEMS, 1u, ns), BLOCK, 0, stream>>>(a);
-                update_depth_match_kernel<<<dim3(mx > qx ? mx : qx, 1u, ns), BLOCK, 0, stream>>>(a);
+                update_depth_match_kernel<<<dim3(mx > mq ? mx : mq, 1u, ns), MATCH_BLOCK, 0, stream>>>(a);
                 TDK_CUDA(cudaGetLastError());
             }
         }
