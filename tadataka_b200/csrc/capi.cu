@@ -37,6 +37,8 @@ struct Arena {
     size_t bytes = 0;
     cudaStream_t streams[NSTREAM] = {nullptr, nullptr, nullptr};
     bool streams_ready = false;
+    int *status_host = nullptr;      // pinned, grow-only: the status words of every chunk of a call
+    size_t status_words = 0;
 };
 Arena g_arena[MAX_DEV];
 std::mutex g_mutex;
@@ -139,8 +141,15 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
         carve_slot((char *)ar->base, slot_bytes * i, C, R, H, W, dbg_argmin != nullptr, out_hist != nullptr, &slots[i]);
 
     const int64_t nchunks = (P + C - 1) / C;
-    int(*st_host)[TDK_ST_WORDS] = nullptr;
-    TDK_CUDA(cudaMallocHost((void **)&st_host, sizeof(int) * TDK_ST_WORDS * nchunks));
+    // pinned landing place for the chunks' status words, kept between calls (a cudaMallocHost per
+    // call costs a device-wide synchronisation)
+    if (ar->status_words < (size_t)(TDK_ST_WORDS * nchunks)) {
+        if (ar->status_host) { TDK_CUDA(cudaFreeHost(ar->status_host)); ar->status_host = nullptr; ar->status_words = 0; }
+        const size_t want = (size_t)TDK_ST_WORDS * (nchunks < 64 ? 64 : nchunks);
+        TDK_CUDA(cudaMallocHost((void **)&ar->status_host, sizeof(int) * want));
+        ar->status_words = want;
+    }
+    int(*st_host)[TDK_ST_WORDS] = reinterpret_cast<int(*)[TDK_ST_WORDS]>(ar->status_host);
     rc = TDK_OK;
     for (int64_t c = 0; c < nchunks && rc == TDK_OK; c++) {
         const int si = (int)(c % nslots);
@@ -190,7 +199,6 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
             }
         }
     }
-    cudaFreeHost(st_host);
     return rc;
 }
 
