@@ -11,10 +11,15 @@ Workload (BASELINE.json configs[1], SURVEY 8d "C2"), per GPU and per step:
     (N > 1: launched by `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N`;
      a plain `python bench.py --gpus N` re-launches itself that way.)
 
-Prints ONE JSON line (rank 0).  `value` = device-resident throughput; `e2e` = the same step through
-the host-pointer C-ABI call (tdk_update_depth_host) from pinned host buffers, H2D and D2H inside
-the timed region; `roofline` = algorithmic bytes of the dominant kernel / its CUDA-event time vs
-the measured HBM peak; `cpu_baseline` = the oracle (CPU restatement of the reference) on the host.
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput of the C2 step (weak scaling:
+every rank runs its own B keyframes per step); at N > 1 every step's depth / variance / flag maps
+are gathered on rank 0 over NCCL inside the timed region (tadataka_b200.sharding.RootGather: the
+transfer of step k overlaps the kernels of step k + 1; flags travel as int8) and the flag
+histograms are all-reduced.  `config.c5` = BASELINE.json configs[4]: 4096 640x480 pairs sharded
+over the N ranks (strong scaling), kernels + the same gather, one total time.  `e2e` = the C2 step
+through the host-pointer C-ABI call (tdk_update_depth_host) from pinned host buffers, H2D and D2H
+inside the timed region; `roofline` = algorithmic bytes of the step / its CUDA-event time vs the
+measured HBM peak; `cpu_baseline` = the oracle (CPU restatement of the reference) on the host.
 """
 import argparse
 import ctypes as C
@@ -40,6 +45,11 @@ UNIT = "pixels/s"
 ALGO_BYTES_PER_PX = 64
 
 
+def workload_name(B):
+    return (f"C2: {B} x (640x480 keyframe vs 8 reference frames by age + Gaussian fusion) per GPU "
+            "per step")
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -50,7 +60,10 @@ def parse():
     ap.add_argument("--distinct", type=int, default=8, help="distinct rendered scenes per GPU")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 measurement")
+    ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 and keyframe-loop measurements")
+    ap.add_argument("--c4-pairs", type=int, default=64, help="1280x720 pairs per launch (BASELINE.json configs[3])")
+    ap.add_argument("--c5-pairs", type=int, default=4096, help="640x480 pairs of the sharded run (configs[4]); 0 = skip")
+    ap.add_argument("--c5-chunk", type=int, default=64, help="pairs per round of the sharded run")
     ap.add_argument("--device-scenes", action="store_true",
                     help="render every keyframe's world on the GPU (tdk_render_scene_dev) instead of in numpy")
     ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (2 sorted [default], 0 two kernels, 1 one kernel)")
@@ -189,20 +202,21 @@ def profiled_traffic():
 # --------------------------------------------------------------------------------- arms
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU path.  The Rust crate cannot be built in this image
-    (no cargo/rustc), so this is the oracle port (oracle/tdk_oracle.c), all host threads."""
+    (no cargo/rustc), so this is the oracle port (oracle/tdk_oracle.c), all host threads, on the
+    same keyframes as the GPU arm's rank 0 (all B of them per step unless that would run for more
+    than about three minutes, in which case every step takes the first S and says so)."""
     if rank != 0:
         return
     import oracle as ora
     threads = host_threads()
-    b = make_workload(0, max(threads, min(args.keyframes, 2 * threads)), args.distinct)
-    P = b["key_img"].shape[0]
-    # size the per-step sample so that the whole run stays within ~2 minutes
+    B = args.keyframes
+    b = make_workload(0, B, args.distinct)
     t0 = time.perf_counter()
-    cpu_pipeline(ora, b, slice(0, min(P, threads)), threads)
-    t_unit = (time.perf_counter() - t0) / min(P, threads) * threads   # thread-seconds per keyframe
+    cpu_pipeline(ora, b, slice(0, min(B, threads)), threads)
+    t_unit = (time.perf_counter() - t0) / min(B, threads) * threads   # thread-seconds per keyframe
     total_steps = args.steps + args.warmup
-    S = int(max(1, min(P, (120.0 * threads / max(t_unit, 1e-6)) / max(total_steps, 1))))
-    if S >= threads:
+    S = int(max(1, min(B, (180.0 * threads / max(t_unit, 1e-6)) / max(total_steps, 1))))
+    if threads <= S < B:
         S = S // threads * threads
     sl = slice(0, S)
     for _ in range(args.warmup):
@@ -212,14 +226,14 @@ def run_reference(args, rank, world):
         cpu_pipeline(ora, b, sl, threads)
     dt = time.perf_counter() - t0
     value = S * H * W * args.steps / dt
-    sample = f"{S} of {args.keyframes} keyframes per step (640x480, 8 refs by age, fusion), {threads} threads"
+    sample = (f"{S} of the step's {B} keyframes (640x480, 8 refs by age, fusion), {threads} threads, "
+              "OpenMP over keyframes")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "ms_per_keyframe": 1e3 * dt / args.steps / S, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"C2: {args.keyframes} x (640x480 keyframe vs 8 reference frames by "
-                               "age + Gaussian fusion) per step", "sample": sample},
+        "config": {"workload": workload_name(B), "keyframes_per_gpu": B, "refs": R, "sample": sample},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -228,10 +242,111 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+NAMES = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
+         "prior_variance"]
+
+
+def run_c5(args, rank, world, dev, barrier):
+    """BASELINE.json configs[4] (SURVEY 8d "C5"): n 640x480 keyframe/reference pairs, set S, seeds
+    5000 + i, sharded over the ranks in contiguous blocks (tadataka_b200.sharding), every pair its
+    own world rendered on its rank by the CUDA ray-caster before the clock starts.  Timed, as one
+    region (device events, max over ranks): the kernels of every round of `chunk` pairs plus the
+    gather of depth / variance / flag maps on rank 0 (overlapping the next round) plus the
+    all-reduce of the flag histogram.  Strong scaling: the total is n pairs at every N."""
+    import torch
+    import torch.distributed as dist
+    from tadataka_b200 import device, scene_device, sharding
+
+    n, chunk = args.c5_pairs, args.c5_chunk
+    if world > 1:
+        rg = sharding.RootGather(n, H, W, chunk, dev)
+    else:
+        rg = None
+    start, stop = sharding.shard_range(n, rank, world)
+    rounds = (max(b - a for a, b in (sharding.shard_range(n, r, world) for r in range(world))) + chunk - 1) // chunk
+    inputs = []
+    for j in range(rounds):
+        a = min(start + j * chunk, stop)
+        z = min(a + chunk, stop)
+        if z > a:
+            t = scene_device.make_keyframes([5000 + i for i in range(a, z)], R=1, H=H, W=W, device=dev,
+                                            ages="ones", per_item_rng=True)
+            params = np.ascontiguousarray(t["params"], dtype=np.float64)
+            inputs.append({k: t[k] for k in NAMES})
+        else:
+            inputs.append(None)
+    if rg is None:
+        out = (torch.empty((n, H, W), dtype=torch.float64, device=dev),
+               torch.empty((n, H, W), dtype=torch.float64, device=dev),
+               torch.empty((n, H, W), dtype=torch.int64, device=dev))
+    hist = torch.zeros((chunk, 10), dtype=torch.int64, device=dev)
+    params = np.ascontiguousarray(scene_params_s(), dtype=np.float64)
+
+    def one_pass(gather):
+        hist.zero_()
+        for j in range(rounds):
+            t = inputs[j]
+            if rg is not None:
+                views = rg.out_views(j)
+            else:
+                a = j * chunk
+                views = tuple(o[a:a + (t["key_img"].shape[0] if t else 0)] for o in out)
+            if t is not None:
+                m = t["key_img"].shape[0]
+                device.update_depth(*(t[k] for k in NAMES), params, check=False, out=views, fuse=False,
+                                    hist=hist[:m])
+            if rg is not None and gather:
+                rg.ship(j)
+        if rg is not None and gather:
+            rg.finish()
+        total = hist.sum(dim=0)
+        if world > 1:
+            dist.all_reduce(total)
+        return total
+
+    res = {}
+    for label, gather in (("compute_only", False), ("total", True)):
+        one_pass(gather)                      # warm-up (allocations, NCCL channels)
+        torch.cuda.synchronize()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        total = one_pass(gather)
+        e1.record()
+        torch.cuda.synchronize()
+        barrier()
+        tm = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        res[label] = float(tm[0])
+    flags = [int(x) for x in total.tolist()]
+    block = {
+        "workload": f"C5: {n} x (640x480 keyframe vs 1 reference frame), sharded over {world} GPU(s) "
+                    f"in rounds of {chunk}, every pair its own CUDA-rendered world",
+        "pairs": n, "scaling": "strong", "total_ms": res["total"], "ms_per_pair": res["total"] / n,
+        "pixels_per_s": n * H * W / (res["total"] * 1e-3),
+        "compute_only_ms": res["compute_only"],
+        "flag_histogram": flags, "success_px": flags[0],
+    }
+    if world > 1:
+        rx = rg.bytes_received / 2 if rank == 0 else 0      # two passes shipped (warm-up + timed)
+        block["gather"] = {
+            "what": "depth f64 + variance f64 + flag int8 of every pair to rank 0 (grouped NCCL send/recv, "
+                    "overlapping the next round's kernels) + all-reduce of the 10-bin histogram",
+            "bytes_into_rank0": rx, "gbs_into_rank0": rx / (res["total"] * 1e-3) / 1e9,
+            "limit": "rank 0's NVLink ingress (900 GB/s nominal per direction)"}
+    return block
+
+
+def scene_params_s():
+    from tadataka_b200 import scene
+    return scene.SET_S["params"]
+
+
 def run_b200(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from tadataka_b200 import _lib, device
+    from tadataka_b200 import _lib, device, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; tadataka_b200 has no CPU path "
@@ -265,15 +380,15 @@ def run_b200(args, rank, world, local_rank):
 
     B = args.keyframes
     plan = args.plan if args.plan >= 0 else (0 if B * H * W <= 640 * 480 else 2)   # what -1 (automatic) resolves to
-    # my kernels per resident step: pair_setup + (sorted plan) sieve, lines, order, match per
-    # sub-batch of <= 64 keyframes / (two kernels) sieve, search / (one kernel) tile
-    launches_per_step = {2: 1 + 4 * ((B + 63) // 64), 0: 3, 1: 2}[plan]
+    # my kernels per resident step: pair_setup + per sub-batch of <= 64 keyframes (sorted plan)
+    # key_prep, sieve, lines, order, match / (two kernels) key_prep, sieve, search / (one kernel) tile
+    nsub = (B + 63) // 64
+    launches_per_step = {2: 1 + 5 * nsub, 0: 1 + 3 * nsub, 1: 2}[plan]
     kernel_desc = {
-        2: "update_depth sieve + lines + order + match kernels (step time, incl. the ~us pair_setup_kernel)",
-        0: "update_depth sieve_kernel + search_kernel (step time, incl. the ~us pair_setup_kernel)",
+        2: "update_depth key_prep + sieve + lines + order + match kernels (step time, incl. the ~us pair_setup_kernel)",
+        0: "update_depth key_prep + sieve + search kernels (step time, incl. the ~us pair_setup_kernel)",
         1: "update_depth_tile_kernel (step time, incl. the ~us pair_setup_kernel)"}[plan]
-    names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth",
-             "prior_variance"]
+    names = NAMES
     if args.device_scenes:
         # every keyframe its own world, rendered by the CUDA ray-caster (csrc/scene.cu); the host
         # copies below only feed the e2e leg and the CPU baseline
@@ -288,22 +403,31 @@ def run_b200(args, rank, world, local_rank):
         pinned = {k: torch.from_numpy(b[k]).pin_memory() for k in names}
         t = {k: pinned[k].to(dev, non_blocking=True) for k in names}
     params = np.ascontiguousarray(b["params"], dtype=np.float64)
+    # N > 1: the results of every step are gathered on rank 0 (RootGather, cyclic over the steps)
+    rg = sharding.RootGather(world * B, H, W, B, dev, cyclic=True) if world > 1 else None
     out = (torch.empty((B, H, W), dtype=torch.float64, device=dev),
            torch.empty((B, H, W), dtype=torch.float64, device=dev),
            torch.empty((B, H, W), dtype=torch.int64, device=dev))
+    hist = torch.zeros((B, 10), dtype=torch.int64, device=dev)
     torch.cuda.synchronize()
 
-    def step():
+    def step(k=0):
+        views = rg.out_views(k) if rg is not None else out
         device.update_depth(t["key_img"], t["key_cam"], t["T_wk"], t["ref_imgs"], t["ref_cams"],
                             t["T_wr"], t["age"], t["prior_depth"], t["prior_variance"], params,
-                            check=False, out=out, fuse=True)
+                            check=False, out=views, fuse=True, hist=hist if rg is not None else False)
+        if rg is not None:
+            rg.ship(k)
 
     def barrier():
         if world > 1:
             dist.barrier()
 
-    for _ in range(max(args.warmup, 3)):
-        step()
+    nwarm = max(args.warmup, 3)
+    for k in range(nwarm):
+        step(k)
+    if rg is not None:
+        rg.finish()
     torch.cuda.synchronize()
     # status of the warm-up launches (age / pose / search-length errors would show here)
     ws = device.workspace(_lib.update_depth_workspace_bytes(B, R, H, W), dev, "update_depth")
@@ -315,15 +439,31 @@ def run_b200(args, rank, world, local_rank):
     barrier()
     torch.cuda.synchronize()
     sampler.start()
+    rx0 = rg.bytes_received if rg is not None else 0
+    hist.zero_()
     ev0.record()
-    for _ in range(args.steps):
-        step()
+    for k in range(args.steps):
+        step(nwarm + k)
+    if rg is not None:
+        rg.finish()
+        hist_total = hist.sum(dim=0)
+        dist.all_reduce(hist_total)
     ev1.record()
     torch.cuda.synchronize()
     sampler.stop_flag = True
     barrier()
     ms_total = ev0.elapsed_time(ev1)
     sampler.join(timeout=1.0)
+    gather_info = None
+    if rg is not None:
+        # the resident maps of this rank's last step (the e2e check below compares with them)
+        out = tuple(x.clone() for x in rg.out_views(nwarm + args.steps - 1)) if rank != 0 else \
+            tuple(x[:B].clone() for x in (rg.depth, rg.variance, rg.flag))
+        rx = rg.bytes_received - rx0
+        gather_info = {"bytes_into_rank0_per_step": rx / max(args.steps, 1),
+                       "what": "depth f64 + variance f64 + flag int8 of every keyframe of every step to rank 0 "
+                               "(grouped NCCL send/recv overlapping the next step) + one all-reduce of the "
+                               "10-bin histograms", "inside_timed_region": True}
 
     # ---- latency of ONE keyframe (8 references) per launch: "ms per keyframe-pair" without batching
     one = {k: t[k][:1].contiguous() for k in names}
@@ -339,24 +479,28 @@ def run_b200(args, rank, world, local_rank):
     torch.cuda.synchronize()
     single_ms = lat0.elapsed_time(lat1) / 50
 
-    # ---- secondary shape (BASELINE.json configs[3] "C4"): 1280x720 TUM-scale pairs, kernel only
+    # ---- secondary shape (BASELINE.json configs[3] "C4"): 64 independent 1280x720 TUM-scale pairs
+    # per launch (every pair its own CUDA-rendered world), kernels only
     c4_ms = None
-    if rank == 0 and not args.no_c4:
-        from tadataka_b200 import scene
-        c4 = scene.stack_keyframes([scene.make_pair(4000 + i, H=720, W=1280, cam=scene.CAM_720P,
-                                                    pset=scene.SET_T) for i in range(8)])
-        c4t = {k: torch.from_numpy(c4[k]).to(dev) for k in names}
-        c4p = np.ascontiguousarray(c4["params"], dtype=np.float64)
+    if rank == 0 and not args.no_c4 and args.c4_pairs > 0:
+        from tadataka_b200 import scene, scene_device
+        n4 = args.c4_pairs
+        c4t = scene_device.make_keyframes([4000 + i for i in range(n4)], R=1, H=720, W=1280, cam=scene.CAM_720P,
+                                          pset=scene.SET_T, device=dev, ages="ones", per_item_rng=True)
+        c4p = np.ascontiguousarray(c4t["params"], dtype=np.float64)
+        c4o = tuple(torch.empty((n4, 720, 1280), dtype=dt, device=dev)
+                    for dt in (torch.float64, torch.float64, torch.int64))
         for _ in range(3):
-            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True)
+            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True, out=c4o)
         torch.cuda.synchronize()
         lat0.record()
         for _ in range(10):
-            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True)
+            device.update_depth(*(c4t[k] for k in names), c4p, check=False, fuse=True, out=c4o)
         lat1.record()
         torch.cuda.synchronize()
-        c4_ms = lat0.elapsed_time(lat1) / 10 / 8
-        del c4t
+        c4_ms = lat0.elapsed_time(lat1) / 10 / n4
+        del c4t, c4o
+        torch.cuda.empty_cache()
 
     # ---- secondary loop (BASELINE.json configs[2] "C3"): the semi_dense_vo keyframe loop over 30
     # frames (increment_age -> propagate -> update_depth + fusion -> regularize, unused reference
@@ -383,6 +527,12 @@ def run_b200(args, rank, world, local_rank):
             torch.cuda.synchronize()
             c3_ms = (time.perf_counter() - t0) * 1e3 / 29
         del mapper
+
+    # ---- C5: the sharded run with the gather inside the clock (all ranks take part)
+    c5 = None
+    if args.c5_pairs > 0:
+        c5 = run_c5(args, rank, world, dev, barrier)
+        torch.cuda.empty_cache()
 
     # ---- e2e: host-pointer C-ABI call, pinned host buffers, copies inside the timed region
     e2e_steps = args.e2e_steps or min(args.steps, 10)
@@ -416,23 +566,11 @@ def run_b200(args, rank, world, local_rank):
     # the e2e path must give the same answer as the resident path
     same = bool(torch.equal(h_out[0], out[0].cpu()) and torch.equal(h_out[2], out[2].cpu()))
 
-    # ---- aggregate over ranks (max time), optional NCCL gather of the maps (never in the loop)
-    gather_ms = None
+    # ---- aggregate over ranks (max time)
     if world > 1:
         tm = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         ms_total, e2e_s = float(tm[0]), float(tm[1])
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        gathered = torch.empty((world, B, H, W), dtype=torch.float64, device=dev)
-        hist = (out[2] == 0).sum().reshape(1)
-        torch.cuda.synchronize()
-        dist.barrier()
-        g0.record()
-        dist.all_gather_into_tensor(gathered, out[0])
-        dist.all_reduce(hist)
-        g1.record()
-        torch.cuda.synchronize()
-        gather_ms = g0.elapsed_time(g1)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -445,22 +583,26 @@ def run_b200(args, rank, world, local_rank):
     achieved = ALGO_BYTES_PER_PX * px_step / (ms_step * 1e-3) / 1e9
     traffic_px = profiled_traffic()
     n_success = int((out[2] == 0).sum())
+    if gather_info is not None:
+        gather_info["gbs_into_rank0"] = gather_info["bytes_into_rank0_per_step"] / (ms_step * 1e-3) / 1e9
+        gather_info["limit"] = "rank 0's NVLink ingress (900 GB/s nominal per direction)"
+        gather_info["success_px_all_ranks"] = int(hist_total[0])
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_keyframe": ms_step / B,
+        "warmup": nwarm, "ms_per_step": ms_step, "ms_per_keyframe": ms_step / B,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {
-            "workload": f"C2: {B} x (640x480 keyframe vs 8 reference frames by age + Gaussian "
-                        "fusion) per GPU per step",
+            "workload": workload_name(B),
             "keyframes_per_gpu": B, "refs": R,
             "distinct_scenes": B if args.device_scenes else min(args.distinct, B),
             "scenes": "CUDA ray-caster" if args.device_scenes else "numpy ray-caster",
             "l2": f"inputs {h2d / 1e9:.2f} GB per step >> 126 MB L2 (no flush needed)",
             "success_px_per_step": n_success, "success_px_per_s": world * n_success / (ms_step * 1e-3),
             "params": [float(x) for x in params], "e2e_matches_resident": same,
-            "nccl_gather_ms": gather_ms, "single_keyframe_launch_ms": single_ms,
-            "c4_720p_ms_per_pair": c4_ms, "c3_vo_loop_ms_per_frame": c3_ms,
+            "nccl_gather": gather_info, "single_keyframe_launch_ms": single_ms,
+            "c4_720p_ms_per_pair": c4_ms, "c4_pairs_per_launch": args.c4_pairs if c4_ms is not None else None,
+            "c3_vo_loop_ms_per_frame": c3_ms, "c5": c5,
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -479,17 +621,17 @@ def run_b200(args, rank, world, local_rank):
     if world == 1 and not args.no_cpu_baseline:
         import oracle as ora
         threads = host_threads()
-        n_kf = min(B, max(threads, 8))
+        n_kf = B
         cpu_maps = []
         v, best, reps = time_cpu(ora, b, n_kf, threads, keep=cpu_maps)
         v1, _, _ = time_cpu(ora, b, 2, 1, budget_s=3.0, max_reps=3)
-        # the CPU run and the GPU run did the same work: identical maps on the sampled keyframes
+        # the CPU run and the GPU run did the same work: identical maps on every keyframe of the step
         same_maps = all(np.array_equal(c, g[:n_kf].cpu().numpy(), equal_nan=True)
                         for c, g in zip(cpu_maps, out))
         line["cpu_baseline"] = {
             "value": v, "unit": UNIT, "cores": threads, "kind": "port", "single_thread_value": v1,
             "maps_identical_to_gpu": bool(same_maps),
-            "sample": f"{n_kf} of the step's {B} keyframes, best of {reps} runs, "
+            "sample": f"all {n_kf} keyframes of the step, best of {reps} runs, "
                       f"{1e3 * best / n_kf:.2f} ms/keyframe, OpenMP over keyframes"}
     print(json.dumps(line), flush=True)
     if world > 1:

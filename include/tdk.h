@@ -82,11 +82,13 @@ const char *tdk_version(void);
  *       (id, var) = fusion(inv(prior_depth), inv(new_depth), prior_variance, new_variance);
  *       depth = inv(id) -- identical to calling tdk_fusion_dev(depth_domain=1) afterwards,
  *       without the second pass over HBM
- *   workspace: device scratch -- status words, per-pair constants, one u32 queue slot per pixel
- *       for the pixels that reach the search, and, for up to 64 keyframes at a time, 137 bytes per
- *       pixel for the search lines (128-byte record, length class, sort position; worst case =
- *       every pixel is searched).  tdk_update_depth_workspace_bytes(P,R,H,W) is the size that runs
- *       fastest (min(P,64) keyframes per sub-batch; 2.7 GB for 64 VGA keyframes);
+ *   workspace: device scratch -- status words, per-pair constants and, for up to 64 keyframes at a
+ *       time (a "sub-batch"; larger launches reuse the arrays sub-batch after sub-batch in stream
+ *       order), per pixel: 4 bytes of queue for the pixels the sieve cannot decide, a 4-byte f32 copy
+ *       of the key image (the sieve's certified rejection reads it), and 133 bytes for
+ *       the search lines (128-byte record, length class, sort position; worst case = every pixel is
+ *       searched).  tdk_update_depth_workspace_bytes(P,R,H,W) is the size that runs fastest
+ *       (min(P,64) keyframes per sub-batch; 2.8 GB for 64 VGA keyframes);
  *       tdk_update_depth_workspace_bytes_min(P,R,H,W) is the least that is accepted (one keyframe
  *       per sub-batch); anything in between is used as far as it goes
  *
@@ -149,13 +151,14 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 void *stream);
 
 /* Tuning knob with no counterpart in the reference: how update_depth is mapped onto kernels.
- * 2 = a sieve over all pixels that queues the survivors of the gradient test in the workspace, a
- * kernel that sets up their search lines, a counting sort of the lines by length, and a search
- * kernel in which every warp walks 32 lines of equal length; 0 = the sieve, then one search kernel
- * over 256 queued pixels per CTA (smaller workspace: 4 bytes per pixel); 1 = one kernel, each CTA
- * compacts and searches its own 64x4 tile (what tdk_update_depth_static_dev runs); -1 (default) =
- * 0 for launches of at most 640x480 pixels in total, 2 for larger ones.
- * Results do not depend on it. */
+ * 2 = an f32 copy of the key images, a sieve over all pixels that gives every pixel it can decide
+ * for certain its final values and queues the others in the workspace, a kernel that runs the exact
+ * prefix of `estimate` on the queued pixels and sets up their search lines, a counting sort of the
+ * lines by length, and a search kernel in which every warp walks 32 lines of equal length; 0 = the
+ * copy and the sieve, then one kernel over 256 queued pixels per CTA (smaller workspace: 8 bytes
+ * per pixel); 1 = one kernel, each CTA runs the exact path on its own 64x4 tile (what
+ * tdk_update_depth_static_dev runs); -1 (default) = 0 for launches of at most 640x480 pixels in
+ * total, 2 for larger ones.  Results do not depend on it. */
 int tdk_set_kernel_plan(int plan);
 
 /* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,
@@ -230,6 +233,74 @@ int tdk_propagate_age_dev(const double *T10, const double *cam0, const double *c
                           double default_variance, double uncertaintity_bias, double *depth1,
                           double *variance1, uint64_t *age1, void *workspace, size_t workspace_bytes,
                           void *stream);
+
+/* Host-pointer forms of the companions: what a numpy caller of the reference binds
+ * (rust_bindings.semi_dense.increment_age / propagate, src/py/semi_dense.rs:35-51,189-218: numpy in,
+ * numpy out, one call; fusion.rs:13-42 and regularization.rs:29-64 for the two the reference keeps
+ * internal).  Arguments as the *_dev forms without workspace and stream; host buffers may be
+ * pageable or pinned; the call stages through the per-device arena and returns when the results
+ * are in host memory.  flag may be NULL in tdk_fusion_host. */
+int tdk_increment_age_host(const uint64_t *age0, const double *cam0, const double *cam1,
+                           const double *T10, const double *depth0, int64_t P, int64_t H, int64_t W,
+                           uint64_t *age1);
+int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1,
+                       const double *depth0, const double *variance0, int64_t P, int64_t H, int64_t W,
+                       double default_depth, double default_variance, double uncertaintity_bias,
+                       double *depth1, double *variance1);
+int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, const double *var2,
+                    const int64_t *flag, int64_t n, int depth_domain, double *mu, double *var);
+int tdk_regularize_host(const double *depth, const double *variance, const int64_t *flag, int64_t P,
+                        int64_t H, int64_t W, double *out_depth);
+
+/* ------------------------------------------------------------------ keyframe loop
+ * The reference's caller keeps the maps and the reference frames in numpy and calls the extension
+ * three times per frame (examples/semi_dense_vo.py:185-203: increment_age, propagate, update_depth,
+ * refframes.append; Frame copies every image once more, src/py/semi_dense.rs:53-67).  tdk_mapper is
+ * that loop with everything resident in HBM behind one call per frame; no counterpart in the
+ * reference.
+ *   - all device memory is ONE caller-owned arena of tdk_mapper_arena_bytes(H, W, capacity) bytes:
+ *     the ring of reference images (capacity frames, contiguous, so update_depth runs without
+ *     pointer tables), their cameras and poses, two sets of maps, scratch;
+ *   - frames arrive as HOST images: TDK_IMAGE_F64 [H,W] f64 gray (what Frame takes),
+ *     TDK_IMAGE_U8 [H,W] 8-bit gray (v / 255), TDK_IMAGE_RGB8 [H,W,3] / TDK_IMAGE_RGBA8 [H,W,4]
+ *     8-bit colour, converted on the device with the luma the reference's dataset loaders apply
+ *     (skimage rgb2gray, tadataka/dataset/new_tsukuba.py:85-86):
+ *     ((R/255) 0.2125 + (G/255) 0.7154) + (B/255) 0.0721, every operation rounded, alpha dropped;
+ *   - tdk_mapper_reset: first frame, age 0, depth / variance from the host maps given or, if NULL,
+ *     the defaults (semi_dense_vo.py:210-219);
+ *   - tdk_mapper_track: next frame with its pose T_wf (world <- frame) and T10 = inv(T_wf) * T_w(previous)
+ *     (the caller computes it, as the reference's loop does): propagate + increment_age, update_depth
+ *     against every frame of the ring [fuse_on_success] [regularize], append the frame.  Enqueues
+ *     on the mapper's stream and returns without waiting for the GPU; errors of the kind
+ *     tdk_update_depth_status reports (age, singular pose, search length) surface in the NEXT
+ *     call or in tdk_mapper_sync;
+ *   - prune != 0: frames older than the largest age on the map are dropped from the ring (the
+ *     reference's TODO, semi_dense_vo.py:202); results do not change, the ring stops growing;
+ *     without pruning (or with too small a capacity) a full ring makes track return
+ *     TDK_ERR_WORKSPACE;
+ *   - tdk_mapper_sync waits for the stream and reports a pending error; tdk_mapper_prune counts the
+ *     ages of the current map and drops the unused frames at once; tdk_mapper_state gives the
+ *     number of frames held and the byte offsets, inside the arena, of the current depth / variance
+ *     (f64), age (u64) and flag (i64) maps [H,W] and of the ring, whose live window starts at frame
+ *     *ring_start. */
+enum { TDK_IMAGE_F64 = 0, TDK_IMAGE_U8 = 1, TDK_IMAGE_RGB8 = 2, TDK_IMAGE_RGBA8 = 3 };
+typedef struct tdk_mapper tdk_mapper;
+size_t tdk_mapper_arena_bytes(int64_t H, int64_t W, int64_t capacity);
+int tdk_mapper_create(void *arena, size_t arena_bytes, int64_t H, int64_t W, int64_t capacity,
+                      const double *params, double default_depth, double default_variance,
+                      double uncertaintity_bias, int fuse_on_success, int regularize, int prune,
+                      void *stream, tdk_mapper **out);
+void tdk_mapper_destroy(tdk_mapper *m);
+int tdk_mapper_reset(tdk_mapper *m, const void *image, int image_format, const double *cam,
+                     const double *T_wf, const double *depth_map, const double *variance_map);
+int tdk_mapper_track(tdk_mapper *m, const void *image, int image_format, const double *cam,
+                     const double *T_wf, const double *T10);
+int tdk_mapper_sync(tdk_mapper *m);
+/* census of the current age map and pruning in one step (waits for the device); what track() does
+ * one frame late when prune != 0 */
+int tdk_mapper_prune(tdk_mapper *m);
+int tdk_mapper_state(tdk_mapper *m, int64_t *n_frames, size_t *depth_off, size_t *variance_off,
+                     size_t *age_off, size_t *flag_off, size_t *ring_off, int64_t *ring_start);
 
 /* ------------------------------------------------------------------ helpers on the drop-in surface
  * rust_bindings.warp.warp_vecs        (src/py/warp.rs:53-67   -> src/warp.rs:31-50)

@@ -61,6 +61,21 @@ propagate_dev = _sig("tdk_propagate_dev", C.c_int, P, P, P, P, P, I64, I64, I64,
                      SZ, P)
 propagate_age_dev = _sig("tdk_propagate_age_dev", C.c_int, P, P, P, P, P, P, I64, I64, I64, D, D, D, P, P, P, P,
                          SZ, P)
+increment_age_host = _sig("tdk_increment_age_host", C.c_int, P, P, P, P, P, I64, I64, I64, P)
+propagate_host = _sig("tdk_propagate_host", C.c_int, P, P, P, P, P, I64, I64, I64, D, D, D, P, P)
+fusion_host = _sig("tdk_fusion_host", C.c_int, P, P, P, P, P, I64, C.c_int, P, P)
+regularize_host = _sig("tdk_regularize_host", C.c_int, P, P, P, I64, I64, I64, P)
+mapper_arena_bytes = _sig("tdk_mapper_arena_bytes", SZ, I64, I64, I64)
+mapper_create = _sig("tdk_mapper_create", C.c_int, P, SZ, I64, I64, I64, P, D, D, D, C.c_int, C.c_int, C.c_int, P,
+                     C.POINTER(C.c_void_p))
+mapper_destroy = _sig("tdk_mapper_destroy", None, P)
+mapper_reset = _sig("tdk_mapper_reset", C.c_int, P, P, C.c_int, P, P, P, P)
+mapper_track = _sig("tdk_mapper_track", C.c_int, P, P, C.c_int, P, P, P)
+mapper_sync = _sig("tdk_mapper_sync", C.c_int, P)
+mapper_prune = _sig("tdk_mapper_prune", C.c_int, P)
+mapper_state = _sig("tdk_mapper_state", C.c_int, P, C.POINTER(I64), C.POINTER(SZ), C.POINTER(SZ), C.POINTER(SZ),
+                    C.POINTER(SZ), C.POINTER(SZ), C.POINTER(I64))
+IMAGE_F64, IMAGE_U8, IMAGE_RGB8, IMAGE_RGBA8 = 0, 1, 2, 3
 warp_vecs_dev = _sig("tdk_warp_vecs_dev", C.c_int, P, P, P, I64, P, P, P)
 interpolate_dev = _sig("tdk_interpolate_dev", C.c_int, P, I64, I64, P, I64, P, P, P)
 project_vecs_dev = _sig("tdk_project_vecs_dev", C.c_int, P, I64, P, P)
@@ -92,6 +107,9 @@ EXPORTS = [
     "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev", "tdk_propagate_age_dev", "tdk_sqrt_threshold",
     "tdk_image_gradient_dev", "tdk_dvo_normal_equations_dev", "tdk_dvo_student_t_dev",
     "tdk_dvo_photometric_error_dev",
+    "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
+    "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
+    "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",
 ]
 
 

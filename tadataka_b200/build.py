@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libtdk_b200.so")
-SOURCES = ["update_depth.cu", "companions.cu", "helpers.cu", "dvo.cu", "scene.cu", "capi.cu"]
+SOURCES = ["update_depth.cu", "companions.cu", "helpers.cu", "dvo.cu", "scene.cu", "mapper.cu", "capi.cu"]
 HEADERS = [os.path.join(CSRC, "tdk_common.cuh"),
            os.path.join(os.path.dirname(HERE), "include", "tdk.h")]
 

@@ -41,7 +41,14 @@ struct Arena {
     size_t status_words = 0;
 };
 Arena g_arena[MAX_DEV];
-std::mutex g_mutex;
+std::mutex g_mutex[MAX_DEV];   // one per device: host-pointer calls on different GPUs do not serialise
+
+int current_device(int *dev)
+{
+    TDK_CUDA(cudaGetDevice(dev));
+    if (*dev < 0 || *dev >= MAX_DEV) { tdk_set_error("device index %d out of range", *dev); return TDK_ERR_INVALID; }
+    return TDK_OK;
+}
 
 size_t up256(size_t v) { return (v + 255) / 256 * 256; }
 
@@ -124,7 +131,10 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
         tdk_set_error("tdk_update_depth_host: bad sizes");
         return TDK_ERR_INVALID;
     }
-    std::lock_guard<std::mutex> lock(g_mutex);
+    int dev = 0;
+    int rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
     const size_t hw = (size_t)H * W;
     // chunk = as many keyframes as fit ~96 MB of staged input, so copies and kernels overlap
     const size_t in_per_key = (size_t)(1 + R + 3) * hw * 8;
@@ -134,7 +144,7 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
     const int nslots = (int)((P + C - 1) / C < NSTREAM ? (P + C - 1) / C : NSTREAM);
     const size_t slot_bytes = carve_slot(nullptr, 0, C, R, H, W, dbg_argmin != nullptr, out_hist != nullptr, nullptr);
     Arena *ar = nullptr;
-    int rc = arena_get(slot_bytes * nslots, &ar);
+    rc = arena_get(slot_bytes * nslots, &ar);
     if (rc != TDK_OK) return rc;
     Slot slots[NSTREAM];
     for (int i = 0; i < nslots; i++)
@@ -212,10 +222,38 @@ int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double pri
         tdk_set_error("tdk_estimate_debug_host: null pointer argument");
         return TDK_ERR_INVALID;
     }
-    if (H <= 0 || W <= 0 || u_key[0] < 0 || u_key[0] >= W || u_key[1] < 0 || u_key[1] >= H) {
-        tdk_set_error("tdk_estimate_debug_host: u_key (%lld,%lld) outside the %lldx%lld image",
-                      (long long)u_key[0], (long long)u_key[1], (long long)W, (long long)H);
-        return TDK_ERR_RANGE;
+    if (H <= 0 || W <= 0 || !(params[4] > 0.)) {
+        tdk_set_error("tdk_estimate_debug_host: bad image size or ref_step_size");
+        return TDK_ERR_INVALID;
+    }
+    if (u_key[0] < 0 || u_key[0] >= W || u_key[1] < 0 || u_key[1] >= H) {
+        // The reference evaluates estimate() for any u_key (src/py/semi_dense.rs:126-155): outside the
+        // image it ends at KEY_OUT_OF_RANGE unless an earlier test fails; the prior is echoed.
+        int dev = 0, rc = current_device(&dev);
+        if (rc != TDK_OK) return rc;
+        std::lock_guard<std::mutex> lock(g_mutex[dev]);
+        Arena *ar = nullptr;
+        if ((rc = arena_get(4096, &ar)) != TDK_OK) return rc;
+        char *base = (char *)ar->base;
+        double *d_in = (double *)base;              // key_cam 4, T_wk 16, ref_cam 4, T_wr 16
+        int *d_flag = (int *)(base + 512);
+        cudaStream_t st = ar->streams[0];
+        double h_in[40];
+        memcpy(h_in, key_cam, 32); memcpy(h_in + 4, T_wk, 128); memcpy(h_in + 20, ref_cam, 32); memcpy(h_in + 24, T_wr, 128);
+        TDK_CUDA(cudaMemcpyAsync(d_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, st));
+        rc = tdk_estimate_outside_dev(d_in, d_in + 4, d_in + 20, d_in + 24, params, H, W, u_key[0], u_key[1],
+                                      prior_depth, prior_variance, d_flag, base + 1024, st);
+        if (rc != TDK_OK) return rc;
+        int h[1 + TDK_ST_WORDS];
+        TDK_CUDA(cudaMemcpyAsync(h, d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+        TDK_CUDA(cudaMemcpyAsync(h + 1, base + 1024, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, st));
+        TDK_CUDA(cudaStreamSynchronize(st));
+        if (h[1 + TDK_ST_SINGULAR]) { tdk_set_error("a reference pose T_wr is singular"); return TDK_ERR_SINGULAR; }
+        *out_flag = h[0];
+        out[0] = prior_depth;
+        out[1] = prior_variance;
+        if (dbg) dbg[0] = -1;
+        return TDK_OK;
     }
     // One-pixel update: age 1 at u_key, 0 elsewhere, through the same kernel as the full map.
     const size_t hw = (size_t)H * W, at = (size_t)u_key[1] * W + u_key[0];
@@ -243,6 +281,141 @@ int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double pri
     }
     free(age); free(pd); free(pv); free(od); free(ov); free(of); free(arg);
     return rc;
+}
+
+// ---- host-pointer forms of the companions: copy in, run the *_dev entry point, copy out, one
+// stream of the per-device arena, returns when the results are in host memory.
+namespace {
+struct Stage {
+    Arena *ar = nullptr;
+    cudaStream_t st = nullptr;
+    size_t off = 0;
+    void *take(size_t bytes) { void *p = (char *)ar->base + off; off += up256(bytes); return p; }
+};
+int stage_open(size_t bytes, Stage *s)
+{
+    int rc = arena_get(bytes, &s->ar);
+    if (rc != TDK_OK) return rc;
+    s->st = s->ar->streams[0];
+    s->off = 0;
+    return TDK_OK;
+}
+int up(Stage &s, void *dst, const void *src, size_t bytes)
+{
+    return tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s.st), "H2D");
+}
+int down(Stage &s, void *dst, const void *src, size_t bytes)
+{
+    return tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s.st), "D2H");
+}
+#define TDK_RC(call) do { rc = (call); if (rc != TDK_OK) return rc; } while (0)
+}  // namespace
+
+int tdk_increment_age_host(const uint64_t *age0, const double *cam0, const double *cam1, const double *T10,
+                           const double *depth0, int64_t P, int64_t H, int64_t W, uint64_t *age1)
+{
+    if (!age0 || !cam0 || !cam1 || !T10 || !depth0 || !age1 || P <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_increment_age_host: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t n = (size_t)P * H * W, wsb = tdk_increment_age_workspace_bytes(P, H, W);
+    Stage s;
+    TDK_RC(stage_open(up256(n * 8) * 3 + up256(P * 32) * 2 + up256(P * 128) + up256(wsb), &s));
+    uint64_t *d_age0 = (uint64_t *)s.take(n * 8), *d_age1 = (uint64_t *)s.take(n * 8);
+    double *d_depth = (double *)s.take(n * 8), *d_c0 = (double *)s.take(P * 32), *d_c1 = (double *)s.take(P * 32);
+    double *d_T = (double *)s.take(P * 128);
+    void *ws = s.take(wsb);
+    TDK_RC(up(s, d_age0, age0, n * 8));
+    TDK_RC(up(s, d_depth, depth0, n * 8));
+    TDK_RC(up(s, d_c0, cam0, P * 32));
+    TDK_RC(up(s, d_c1, cam1, P * 32));
+    TDK_RC(up(s, d_T, T10, P * 128));
+    TDK_RC(tdk_increment_age_dev(d_age0, d_c0, d_c1, d_T, d_depth, P, H, W, d_age1, ws, wsb, s.st));
+    TDK_RC(down(s, age1, d_age1, n * 8));
+    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+}
+
+int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1, const double *depth0,
+                       const double *variance0, int64_t P, int64_t H, int64_t W, double default_depth,
+                       double default_variance, double uncertaintity_bias, double *depth1, double *variance1)
+{
+    if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || P <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_propagate_host: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t n = (size_t)P * H * W, wsb = tdk_propagate_workspace_bytes(P, H, W);
+    Stage s;
+    TDK_RC(stage_open(up256(n * 8) * 4 + up256(P * 32) * 2 + up256(P * 128) + up256(wsb), &s));
+    double *d_d0 = (double *)s.take(n * 8), *d_v0 = (double *)s.take(n * 8);
+    double *d_d1 = (double *)s.take(n * 8), *d_v1 = (double *)s.take(n * 8);
+    double *d_c0 = (double *)s.take(P * 32), *d_c1 = (double *)s.take(P * 32), *d_T = (double *)s.take(P * 128);
+    void *ws = s.take(wsb);
+    TDK_RC(up(s, d_d0, depth0, n * 8));
+    TDK_RC(up(s, d_v0, variance0, n * 8));
+    TDK_RC(up(s, d_c0, cam0, P * 32));
+    TDK_RC(up(s, d_c1, cam1, P * 32));
+    TDK_RC(up(s, d_T, T10, P * 128));
+    TDK_RC(tdk_propagate_dev(d_T, d_c0, d_c1, d_d0, d_v0, P, H, W, default_depth, default_variance,
+                             uncertaintity_bias, d_d1, d_v1, ws, wsb, s.st));
+    TDK_RC(down(s, depth1, d_d1, n * 8));
+    TDK_RC(down(s, variance1, d_v1, n * 8));
+    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+}
+
+int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, const double *var2,
+                    const int64_t *flag, int64_t n, int depth_domain, double *mu, double *var)
+{
+    if (!mu1 || !mu2 || !var1 || !var2 || !mu || !var || n <= 0) {
+        tdk_set_error("tdk_fusion_host: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t b = (size_t)n * 8;
+    Stage s;
+    TDK_RC(stage_open(up256(b) * 7, &s));
+    double *d_m1 = (double *)s.take(b), *d_m2 = (double *)s.take(b), *d_v1 = (double *)s.take(b), *d_v2 = (double *)s.take(b);
+    double *d_mu = (double *)s.take(b), *d_var = (double *)s.take(b);
+    int64_t *d_f = flag ? (int64_t *)s.take(b) : nullptr;
+    TDK_RC(up(s, d_m1, mu1, b));
+    TDK_RC(up(s, d_m2, mu2, b));
+    TDK_RC(up(s, d_v1, var1, b));
+    TDK_RC(up(s, d_v2, var2, b));
+    if (flag) TDK_RC(up(s, d_f, flag, b));
+    TDK_RC(tdk_fusion_dev(d_m1, d_m2, d_v1, d_v2, d_f, n, depth_domain, d_mu, d_var, s.st));
+    TDK_RC(down(s, mu, d_mu, b));
+    TDK_RC(down(s, var, d_var, b));
+    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+}
+
+int tdk_regularize_host(const double *depth, const double *variance, const int64_t *flag, int64_t P, int64_t H,
+                        int64_t W, double *out_depth)
+{
+    if (!depth || !variance || !flag || !out_depth || P <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_regularize_host: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t b = (size_t)P * H * W * 8;
+    Stage s;
+    TDK_RC(stage_open(up256(b) * 4, &s));
+    double *d_d = (double *)s.take(b), *d_v = (double *)s.take(b), *d_o = (double *)s.take(b);
+    int64_t *d_f = (int64_t *)s.take(b);
+    TDK_RC(up(s, d_d, depth, b));
+    TDK_RC(up(s, d_v, variance, b));
+    TDK_RC(up(s, d_f, flag, b));
+    TDK_RC(tdk_regularize_dev(d_d, d_v, d_f, P, H, W, d_o, s.st));
+    TDK_RC(down(s, out_depth, d_o, b));
+    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
 }
 
 }  // extern "C"

@@ -2,16 +2,21 @@
 // Replaces src/semi_dense/semi_dense.rs:91-234 of the reference (see include/tdk.h).
 //
 // pair_setup_kernel computes, once per (keyframe, reference), what the reference recomputes for
-// every pixel.  The per-pixel pipeline is cut into four phases (A1 sieve, A2 line set-up, B search,
-// C triangulation + variance; see the block comment further down) and arranged in two plans:
-//   two kernels (default): sieve_kernel runs A1 on every pixel (~85-98 % of pixels finish there) and
-//       appends the survivors to a per-keyframe queue in the workspace; search_kernel takes 256
-//       queued pixels per CTA, so A2 / B / C run with every thread of the CTA busy;
-//   one kernel: a CTA owns a 64x4 tile, compacts its own candidates in shared memory and runs all
-//       phases; needs no queue (this is what the workspace-free entry point uses).
-// Both produce bit-identical results.
+// every pixel.  The per-pixel pipeline is cut into phases (A0 certified sieve, A1 exact prefix up to
+// the gradient test, A2 line set-up, B search, C triangulation + variance; see the block comments
+// further down) and arranged in three plans:
+//   sorted (default for batches): key_prep_kernel (f32 copy of the key images), sieve_kernel (A0 on
+//       every pixel: 80-96 % of the pixels get their final values there, the undecided ones go to a
+//       per-keyframe queue), lines_kernel (A1 + A2 per queued pixel, a 128-byte line record per
+//       survivor), order_kernel (counting sort by line length), match_kernel (B + C);
+//   two kernels (single small keyframes): key_prep, sieve, then search_kernel takes 256 queued pixels
+//       per CTA and runs A1 / A2 / B / C;
+//   one kernel: a CTA owns a 64x4 tile, runs the exact A1 on every pixel, compacts its own candidates
+//       in shared memory and runs all phases; needs no queue (what the workspace-free entry point uses).
+// All three produce bit-identical results.
 #include <math.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "tdk_common.cuh"
@@ -45,21 +50,27 @@ struct UpdArgs {
     int *dbg;
     unsigned long long *hist;
     int *status;
-    unsigned int *cand;         // queue plans: [P, H*W] candidate pixel indices
-    unsigned int *cand_count;   // queue plans: [P] queue lengths
-    // sorted plan, all indexed by the keyframe's position in the current sub-batch (blockIdx.z):
-    double2 *rec;               // [S, H*W] 128 bytes per queue slot: phase A1 results written by the sieve
-                                //           (field-major inside each chunk of 256 slots), replaced by
-                                //           the line records (one 128-byte record per slot) in lines_kernel
+    // queue plans, all indexed by the keyframe's position in the current sub-batch (blockIdx.z):
+    unsigned int *cand;         // [S, H*W] queue of the pixels the sieve could not decide
+    unsigned int *cand_count;   // [S] queue lengths
+    const float *img32;         // [S, H*W] f32 copy of the key images (key_prep_kernel)
+    const unsigned int *amax;   // [S] bits of a float >= max |key image| (+inf if a value is not finite)
+    // sorted plan:
+    double2 *rec;               // [S, H*W] one 128-byte line record per queue slot (lines_kernel)
     unsigned char *len_class;   // [S, H*W] min(line length, 63) per queue slot, 0 = dropped in A2
     unsigned int *order;        // [S, H*W] queue slots of the live lines, longest class first
     unsigned int *len_hist;     // [S, 64] lines per length class
     unsigned int *len_cursor;   // [S, 64] slots handed out per class while `order` is filled
     size_t rec_stride;          // slots per keyframe in rec: H*W rounded up to whole chunks of 256
     int warp_budget;            // match_kernel: warps per keyframe that can be resident at once
-    int p0;                     // first keyframe of the sub-batch (blockIdx.z + p0 indexes maps, keys, pairs, cand)
+    int p0;                     // first keyframe of the sub-batch (blockIdx.z + p0 indexes maps, keys, pairs)
     double vmin, vmax, geo, photo, step, min_grad;
     double min_grad_sq;         // smallest s with sqrt(s) >= min_grad (NaN if min_grad is NaN)
+    // phase A0 (certified sieve), see phase_a0()
+    double cert_m;              // min_grad * (1 - 1e-5), or -1 if min_grad is not a positive number
+    double cert_e;              // bound on |f32 difference - reference difference| per unit of max |image|
+    float cert_lo, cert_xhi, cert_yhi;      // a coordinate in [lo, hi] is inside the image for certain
+    float cert_out, cert_xout, cert_yout;   // a coordinate < out or > [xy]out is outside for certain
     int P, R, H, W, tiles_x, tiles_y, fuse;
 };
 
@@ -285,6 +296,110 @@ __device__ __forceinline__ int phase_a1(const UpdArgs &a, const TdkKeyConst &key
     const double gr = sr == sf ? gf : sqrt(sr);
     o.kstep = kstep; o.gf = gf; o.gr = gr; o.idp = idp; o.r = r;
     return 1;
+}
+
+// =============================================================================================
+// Phase A0: the certified sieve.  Most pixels (80-96 %) end at the gradient test of phase A1 after
+// paying for five exact f64 bilinear samples, two square roots and eight IEEE divisions.  A0 decides
+// them from a cheap approximation whose distance to the reference's f64 values is bounded, and
+// finishes a pixel only when the bound leaves no doubt; everything else goes to the exact path, so
+// the outputs stay bit-identical.
+//
+// Exact, as in A1: inv(d), check_args, inv(inv(d)) (what a failed pixel stores), ref_z and its sign.
+// Approximate from there:
+//   key_step  idp * (rz + eps) * step instead of (idp / inv(rz)) * step: relative distance <= 2^-50;
+//   direction (x_key - e_key) * rsqrt(|.|^2), rsqrt = MUFU.RSQ64H + two Newton steps: <= 2^-30;
+//   a = (float)(key_step * dir * f): the step between two samples in pixels, per axis;
+//   sample coordinates fmaf(k - 2, a, (float)pixel): for half segments below CERT_HMAX pixels each is
+//       within delta = (2 CERT_HMAX + max(W, H)) * 2^-22 pixels of the reference's f64 coordinate
+//       (2^-24 relative for the conversion of a, half an ulp of a float below W + CERT_HMAX for the
+//       sum, 2^-40 (W + CERT_HMAX) for everything rounded in f64; the bound used is 4x that sum);
+//   samples   f32 bilinear on the f32 copy of the key image.  With A = max |image|: moving a
+//       coordinate by delta moves the (continuous, piecewise bilinear) interpolant by at most 2 A delta
+//       per axis; the f32 copy is within 2^-24 A; the f32 lerps round 12 times at most 2^-24 A; the
+//       reference's own f64 rounding is below 2^-49 A.  So |s32 - s_ref| <= (4 delta + 16 * 2^-24) A,
+//       and a difference of two neighbouring samples is within e = 2 (4 delta + 16 * 2^-24) A + 2^-22 A
+//       of the reference's (cert_e = e / A is computed by launch()).
+// Decisions:
+//   range test (image_range.rs:45-57; flag -2 precedes -6): the outer points 0 and 4 bound the other
+//       three.  Both inside [max(delta, 1e-3), size - 1 - max(delta, 1e-3)]: in range for certain.
+//       One of them beyond the image by more than that margin: KEY_OUT_OF_RANGE for certain.
+//   gradient test (semi_dense.rs:129-136): the reference's sum of squared differences, in either
+//       summation order, is at most (sqrt(S32) (1 + 2^-21) + 2 e)^2 (1 + 2^-49) (triangle inequality
+//       in R^4), so S32 < ((min_grad (1 - 1e-5) - 2 e)^2 (1 - 1e-5), rounded down to f32) certifies
+//       INSUFFICIENT_GRADIENT.  NaN or Inf anywhere fails every comparison and falls through.
+// tools/sieve_model.py restates this in numpy and checks it against the oracle on the CPU.
+constexpr float CERT_HMAX = 128.f;   // longest half segment (2 key steps, in pixels) the cheap path takes
+
+__device__ __forceinline__ double rsqrt_2newton(double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));   // MUFU.RSQ64H
+    const double h = 0.5 * x;
+    y = y * __fma_rn(-h, y * y, 1.5);
+    y = y * __fma_rn(-h, y * y, 1.5);
+    return y;
+}
+
+// f32 bilinear sample; (cx, cy) inside [0, W-1) x [0, H-1) so that all four taps exist
+__device__ __forceinline__ float sample32(const float *__restrict__ img, int W, float cx, float cy)
+{
+    const int ix = __float2int_rd(cx), iy = __float2int_rd(cy);
+    const float wx = cx - (float)ix, wy = cy - (float)iy;
+    const float *__restrict__ p = img + iy * W + ix;
+    const float a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + W), d = __ldg(p + W + 1);
+    const float top = __fmaf_rn(wx, b - a, a), bot = __fmaf_rn(wx, d - c, c);
+    return __fmaf_rn(wy, bot - top, top);
+}
+
+// Phase A0 for pixel (x, y) with prior (d, v) and 0 < age <= R.  Returns a final flag (<= 0) or
+// 1 = undecided (the exact path has to look at it).  out_d as in phase_a1.  thr2: the keyframe's
+// threshold on the f32 sum of squared differences (negative: certify nothing).
+__device__ __forceinline__ int phase_a0(const UpdArgs &a, const TdkKeyConst &key, const float *__restrict__ img32,
+                                        int p, int x, int y, double xk, double yk, uint64_t age, double d,
+                                        double v, float thr2, double &out_d)
+{
+    out_d = d;
+    const double idp = tdk::inv(d);
+    const int flag = check_args(idp, v, a.vmin, a.vmax);   // semi_dense.rs:209-214
+    if (flag != TDK_FLAG_SUCCESS) return flag;
+    const double kd = tdk::inv(idp);
+    out_d = kd;
+    const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + (a.R - (int)age);
+    const double rz = pc->T[8] * (xk * kd) + pc->T[9] * (yk * kd) + pc->T[10] * (1. * kd) + pc->T[11];
+    if (rz <= 0.) return TDK_FLAG_NEGATIVE_REF_DEPTH;
+    // ---- approximate from here on
+    const double kstep = (idp * (rz + TDK_EPS_INV)) * a.step;
+    const double kdx = xk - pc->ex, kdy = yk - pc->ey;
+    const double rn = rsqrt_2newton(kdx * kdx + kdy * kdy);
+    const float ax = (float)((kstep * (kdx * rn)) * key.fx);
+    const float ay = (float)((kstep * (kdy * rn)) * key.fy);
+    if (!(fabsf(ax) < 0.5f * CERT_HMAX && fabsf(ay) < 0.5f * CERT_HMAX)) return 1;   // too long, or not a number
+    const float xf = (float)x, yf = (float)y;
+    const float x0 = __fmaf_rn(-2.f, ax, xf), y0 = __fmaf_rn(-2.f, ay, yf);
+    const float x4 = __fmaf_rn(2.f, ax, xf), y4 = __fmaf_rn(2.f, ay, yf);
+    const float xlo = fminf(x0, x4), xhi = fmaxf(x0, x4), ylo = fminf(y0, y4), yhi = fmaxf(y0, y4);
+    if (!(xlo >= a.cert_lo && xhi <= a.cert_xhi && ylo >= a.cert_lo && yhi <= a.cert_yhi)) {
+        const bool out = xlo < a.cert_out || xhi > a.cert_xout || ylo < a.cert_out || yhi > a.cert_yout;
+        return out ? TDK_FLAG_KEY_OUT_OF_RANGE : 1;
+    }
+    const int W = a.W;
+    const float s0 = sample32(img32, W, x0, y0);
+    const float s1 = sample32(img32, W, xf - ax, yf - ay);
+    const float s2 = __ldg(img32 + y * W + x);
+    const float s3 = sample32(img32, W, xf + ax, yf + ay);
+    const float s4 = sample32(img32, W, x4, y4);
+    const float d0 = s1 - s0, d1 = s2 - s1, d2 = s3 - s2, d3 = s4 - s3;
+    const float S = __fmaf_rn(d3, d3, __fmaf_rn(d2, d2, __fmaf_rn(d1, d1, d0 * d0)));
+    return S < thr2 ? TDK_FLAG_INSUFFICIENT_GRADIENT : 1;
+}
+
+// The keyframe's threshold for phase_a0 from A = max |key image| (see the block comment above).
+__device__ __forceinline__ float cert_threshold(const UpdArgs &a, unsigned int amax_bits)
+{
+    const double A = (double)__uint_as_float(amax_bits);
+    const double thr = a.cert_m - 2. * (a.cert_e * A);
+    return thr > 0. ? __double2float_rd((thr * thr) * (1. - 1e-5)) : -1.f;   // NaN -> -1
 }
 
 __device__ __forceinline__ void queue_push(CtaQueue &Q, int slot, const A1Result &c, double v, double xk, double yk,
@@ -696,24 +811,41 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
 }
 
 // ---------------------------------------------------------------------------------------------
-// Two-kernel plan.  sieve_kernel runs phase A1 on every pixel, stores the result of every pixel
-// that is finished (and the provisional prior for candidates) and appends the candidates of its
-// tile to the keyframe's queue in global memory.  search_kernel then takes 256 candidates of one
-// keyframe per CTA, so phases A2 / B / C run with every thread busy.
-__device__ __forceinline__ void a1_store(double2 *rec_base, size_t slot, const A1Result &c, double v, int px);   // below, with the sorted plan
+// Queue plans.  key_prep_kernel leaves an f32 copy of every key image of the sub-batch and a bound on
+// its largest magnitude in the workspace; sieve_kernel runs phase A0 on every pixel, stores the
+// final values of every pixel it can decide (and the provisional "failed estimate" values of the
+// others) and appends the undecided pixels of its tile to the keyframe's queue in global memory.
+__global__ void __launch_bounds__(256) key_prep_kernel(const TdkKeyConst *__restrict__ keys, int p0, size_t hw,
+                                                       float *__restrict__ img32, unsigned int *amax)
+{
+    const int pl = blockIdx.y;
+    const double *__restrict__ src = keys[pl + p0].img;
+    float *__restrict__ dst = img32 + (size_t)pl * hw;
+    float m = 0.f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hw; i += (size_t)gridDim.x * blockDim.x) {
+        const double v = __ldg(src + i);
+        dst[i] = (float)v;
+        const float av = __double2float_ru(fabs(v));
+        m = av == av ? fmaxf(m, av) : INFINITY;   // a NaN in the image switches the cheap path off
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+    // non-negative floats order like their bit patterns
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(amax + pl, __float_as_uint(m));
+}
 
 __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kernel(const UpdArgs a)
 {
     __shared__ double s_xk[TILE_W], s_yk[TILE_H];
     __shared__ unsigned int s_hist[10];
+    __shared__ float s_thr2;
 
     const int tid = threadIdx.x;
-    const int p = (int)blockIdx.z + a.p0;
+    const int pl = blockIdx.z, p = pl + a.p0;
     const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
     const TdkKeyConst key = a.keys[p];
-    const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
 
     const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
     const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
@@ -725,41 +857,40 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     if (valid) { age = a.age[pix]; d = a.prior_d[pix]; v = a.prior_v[pix]; }
 
     if (tid < 10) s_hist[tid] = 0;
+    // camera.rs:55-57: x_key depends on the column (row) only -- one division per column (row) of
+    // the tile instead of two per pixel
     if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
     else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
+    else if (tid == TILE_W + TILE_H) s_thr2 = cert_threshold(a, a.amax[pl]);
     __syncthreads();
 
     int flag = TDK_FLAG_NOT_PROCESSED;
-    A1Result c;
     if (valid) {
         double out_d = d;
         if (age != 0) {
             if (age > (uint64_t)a.R) {
                 atomicExch(&a.status[TDK_ST_AGE], 1);
             } else {
-                flag = phase_a1(a, key, p, s_xk[lx], s_yk[ly], age, d, v, wm1, hm1, out_d, c);
+                flag = phase_a0(a, key, a.img32 + (size_t)pl * hw, p, x, y, s_xk[lx], s_yk[ly], age, d, v, s_thr2,
+                                out_d);
             }
         }
-        // candidates get the values a failed estimate keeps; search_kernel overwrites them on success
+        // undecided pixels get the values a failed estimate keeps; the later kernels overwrite the
+        // flag if the exact path fails them and all three values on success
         a.out_d[pix] = out_d;
         a.out_v[pix] = v;
         a.out_f[pix] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
         if (a.dbg) a.dbg[pix] = -1;
         if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
     }
-    // append this warp's candidates to the keyframe's queue: one global atomic per warp, no CTA barrier
+    // append this warp's undecided pixels to the keyframe's queue: one global atomic per warp, no CTA barrier
     const unsigned cmask = __ballot_sync(0xffffffffu, flag == 1);
     if (cmask) {
         const int lane = tid & 31;
         unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(a.cand_count + p, (unsigned int)__popc(cmask));
+        if (lane == 0) base = atomicAdd(a.cand_count + pl, (unsigned int)__popc(cmask));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (flag == 1) {
-            const unsigned int slot = base + __popc(cmask & ((1u << lane) - 1u));
-            a.cand[map_base + slot] = (unsigned int)(y * W + x);
-            // sorted plan: hand the A1 results to lines_kernel through the slot's place in `rec`
-            if (a.rec) a1_store(a.rec, (size_t)blockIdx.z * a.rec_stride + slot, c, v, x | (y << 16));
-        }
+        if (flag == 1) a.cand[(size_t)pl * hw + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
     }
     if (a.hist) {
         __syncthreads();
@@ -774,22 +905,22 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
     __shared__ unsigned int s_hist[10];
 
     const int tid = threadIdx.x;
-    const int p = (int)blockIdx.z + a.p0;
-    const int total = (int)a.cand_count[p];
+    const int pl = blockIdx.z, p = pl + a.p0;
+    const int total = (int)a.cand_count[pl];
     const int W = a.W, H = a.H;
-    const size_t map_base = (size_t)p * H * W;
+    const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
     const TdkKeyConst key = a.keys[p];
     const double wm1 = (double)W - 1., hm1 = (double)H - 1.;
     if (tid < 10) s_hist[tid] = 0;
     __syncthreads();
 
-    // the grid holds a quarter of the keyframe's tiles per keyframe (usually 5-15 % of the pixels
-    // are queued); CTAs stride over the queue in chunks of BLOCK candidates
+    // the grid holds a quarter of the keyframe's tiles per keyframe (usually 5-20 % of the pixels
+    // are queued); CTAs stride over the queue in chunks of BLOCK pixels
     for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
         const int nq = min(BLOCK, total - first);
-        // ---- phase A1 again for this chunk's candidates (same arithmetic, so they all pass again), then A2
+        // ---- the exact phase A1 for this chunk's pixels (the sieve could not decide them), then A2
         if (tid < nq) {
-            const unsigned int li = a.cand[map_base + first + tid];
+            const unsigned int li = a.cand[(size_t)pl * hw + first + tid];
             const int y = (int)(li / (unsigned int)W), x = (int)(li - (unsigned int)y * W);
             const size_t pix = map_base + li;
             const uint64_t age = a.age[pix];
@@ -797,10 +928,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
             const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
             A1Result c;
             double fail_d;
-            phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
-            queue_push(Q, tid, c, v, xk, yk, x, y, tid);
-            const int flag = phase_a2(a, Q, p, tid, wm1, hm1);
-            if (flag != 1) {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
+            int flag = phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
+            Q.n[tid] = 0;
+            if (flag == 1) {
+                queue_push(Q, tid, c, v, xk, yk, x, y, tid);
+                flag = phase_a2(a, Q, p, tid, wm1, hm1);
+            }
+            if (flag != 1) {   // failed in A1 / A2: the sieve's provisional depth / variance stand, only the flag changes
                 a.out_f[pix] = (long long)flag;
                 if (a.hist) atomicAdd(&s_hist[-flag], 1u);
             }
@@ -826,10 +960,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
 }
 
 // ---------------------------------------------------------------------------------------------
-// Sorted plan (default).  The sieve also leaves the phase A1 results of every queued pixel in the
-// workspace; then three kernels per sub-batch of keyframes:
-//   lines_kernel  thread per queued pixel: phase A2, a 128-byte line record into the workspace (in
-//                 place of the A1 results), the line's length class and a per-keyframe histogram;
+// Sorted plan (default).  After the sieve, three kernels per sub-batch of keyframes:
+//   lines_kernel  thread per queued pixel: the exact phases A1 and A2, a 128-byte line record into the
+//                 workspace, the line's length class and a per-keyframe histogram;
 //   order_kernel  counting sort by length class: fills `order` with the live queue slots, longest first;
 //   match_kernel  a warp takes 32 consecutive entries of `order` -- lines of (nearly) equal length --
 //                 and every lane walks its own line exactly as intensities.rs:16-29 does, then runs
@@ -845,28 +978,8 @@ constexpr int LEN_CLASSES = 64;
 #endif
 constexpr int LINES_MIN_CTAS = TDK_LINES_MIN_CTAS, MATCH_MIN_CTAS = TDK_MATCH_MIN_CTAS;
 constexpr int REC_DOUBLE2 = 8;   // 128 bytes per queue slot
-constexpr int REC_DOUBLES = 2 * REC_DOUBLE2;
-constexpr int A1_FIELDS = 11;    // ki[5], kstep, gf, gr, idp, prior variance, {ref | pixel}
-static_assert(A1_FIELDS <= REC_DOUBLES, "the A1 results must fit the slot they share with the line record");
 
 struct RecTail { int n, ref, px, pad; };
-
-// The sieve's hand-over: field f of queue slot s goes to word f * BLOCK + (s % BLOCK) of the chunk of
-// BLOCK slots that s belongs to, so both the sieve's warps (consecutive slots) and lines_kernel
-// (thread t <-> slot first + t) touch consecutive words.
-__device__ __forceinline__ void a1_store(double2 *rec_base, size_t slot, const A1Result &c, double v, int px)
-{
-    double *chunk = reinterpret_cast<double *>(rec_base) + (slot & ~(size_t)(BLOCK - 1)) * REC_DOUBLES;
-    const int j = (int)(slot & (BLOCK - 1));
-#pragma unroll
-    for (int k = 0; k < 5; k++) chunk[k * BLOCK + j] = c.ki[k];
-    chunk[5 * BLOCK + j] = c.kstep;
-    chunk[6 * BLOCK + j] = c.gf;
-    chunk[7 * BLOCK + j] = c.gr;
-    chunk[8 * BLOCK + j] = c.idp;
-    chunk[9 * BLOCK + j] = v;
-    reinterpret_cast<int2 *>(chunk)[10 * BLOCK + j] = make_int2(c.r, px);
-}
 
 __device__ __forceinline__ void record_store(double2 *__restrict__ r, const LineRec &l, int ref, int px, double v)
 {
@@ -888,7 +1001,7 @@ __global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kern
     __shared__ double2 s_rec[BLOCK * REC_PAD];
     const int tid = threadIdx.x;
     const int pl = blockIdx.z, p = pl + a.p0;
-    const int total = (int)a.cand_count[p];
+    const int total = (int)a.cand_count[pl];
     if ((int)blockIdx.x * BLOCK >= total) return;
     const int W = a.W, H = a.H;
     const size_t hw = (size_t)H * W, map_base = (size_t)p * hw, ws_base = (size_t)pl * hw;
@@ -897,40 +1010,29 @@ __global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kern
     const size_t rec_base = (size_t)pl * a.rec_stride;
     if (tid < 10) s_hist[tid] = 0;
     if (tid < LEN_CLASSES) s_len[tid] = 0;
+    __syncthreads();
 
     for (int first = (int)blockIdx.x * BLOCK; first < total; first += (int)gridDim.x * BLOCK) {
         const int i = first + tid;
-        const bool live = i < total;
-        A1Result c;
-        double v = 0.;
-        int px = 0;
-        if (live) {
-            const double *__restrict__ chunk = reinterpret_cast<const double *>(a.rec) + (rec_base + first) * REC_DOUBLES;
-#pragma unroll
-            for (int k = 0; k < 5; k++) c.ki[k] = chunk[k * BLOCK + tid];
-            c.kstep = chunk[5 * BLOCK + tid];
-            c.gf = chunk[6 * BLOCK + tid];
-            c.gr = chunk[7 * BLOCK + tid];
-            c.idp = chunk[8 * BLOCK + tid];
-            v = chunk[9 * BLOCK + tid];
-            const int2 t = reinterpret_cast<const int2 *>(chunk)[10 * BLOCK + tid];
-            c.r = t.x;
-            px = t.y;
-        }
-        __syncthreads();   // every A1 result of this chunk is in registers: the records may overwrite them
-        if (live) {
-            const int x = px & 0xffff, y = px >> 16;
+        if (i < total) {
+            const unsigned int li = a.cand[ws_base + i];
+            const int y = (int)(li / (unsigned int)W), x = (int)(li - (unsigned int)y * W);
+            const size_t pix = map_base + li;
+            const uint64_t age = a.age[pix];
+            const double d = a.prior_d[pix], v = a.prior_v[pix];
             const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
-            const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + c.r;
+            A1Result c;
+            double fail_d;
             LineRec l;
-            const int flag = phase_a2_core(a, pc, xk, yk, v, c, wm1, hm1, l);
+            int flag = phase_a1(a, key, p, xk, yk, age, d, v, wm1, hm1, fail_d, c);
+            if (flag == 1) flag = phase_a2_core(a, a.pairs + (size_t)p * a.R + c.r, xk, yk, v, c, wm1, hm1, l);
             int cls = 0;
             if (flag == 1) {
                 cls = min(l.n, LEN_CLASSES - 1);
-                record_store(s_rec + tid * REC_PAD, l, c.r, px, v);
+                record_store(s_rec + tid * REC_PAD, l, c.r, x | (y << 16), v);
                 atomicAdd(&s_len[cls], 1u);
-            } else {   // dropped in A2: the sieve's provisional depth / variance stand, only the flag changes
-                a.out_f[map_base + (size_t)y * W + x] = (long long)flag;
+            } else {   // failed in A1 / A2: the sieve's provisional depth / variance stand, only the flag changes
+                a.out_f[pix] = (long long)flag;
                 if (a.hist) atomicAdd(&s_hist[-flag], 1u);
             }
             a.len_class[ws_base + i] = (unsigned char)cls;
@@ -944,8 +1046,8 @@ __global__ void __launch_bounds__(BLOCK, LINES_MIN_CTAS) update_depth_lines_kern
             const int idx = it * BLOCK + tid;
             out[idx] = s_rec[(idx >> 3) * REC_PAD + (idx & 7)];
         }
+        __syncthreads();   // s_rec is reused by the next chunk
     }
-    __syncthreads();
     if (tid < LEN_CLASSES && s_len[tid]) atomicAdd(&a.len_hist[pl * LEN_CLASSES + tid], s_len[tid]);
     if (a.hist && tid < 10 && s_hist[tid]) atomicAdd(&a.hist[(size_t)p * 10 + tid], (unsigned long long)s_hist[tid]);
 }
@@ -972,8 +1074,8 @@ __global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs
 {
     __shared__ unsigned int s_start[LEN_CLASSES], s_cnt[LEN_CLASSES], s_off[LEN_CLASSES];
     const int tid = threadIdx.x;
-    const int pl = blockIdx.z, p = pl + a.p0;
-    const int total = (int)a.cand_count[p];
+    const int pl = blockIdx.z;
+    const int total = (int)a.cand_count[pl];
     constexpr int ROUND = BLOCK * ORDER_ITEMS;
     if ((int)blockIdx.x * ROUND >= total) return;
     const size_t ws_base = (size_t)pl * a.H * a.W;   // a multiple of 4 is not guaranteed: byte loads below
@@ -1080,26 +1182,41 @@ __global__ void __launch_bounds__(MATCH_BLOCK, MATCH_MIN_CTAS * BLOCK / MATCH_BL
 }
 
 // ---------------------------------------------------------------------------------------------
+// estimate_debug_ for a pixel OUTSIDE the image (src/py/semi_dense.rs:126-155 accepts any u_key): the
+// exact phase A1 on that one pixel.  Its centre sample is the pixel itself, so the range test
+// (flag -2) fails before any image access unless an earlier test (-7, -1, -8) already did.
+__global__ void estimate_outside_kernel(const UpdArgs a, long long x, long long y, double d, double v, int *out_flag)
+{
+    const TdkKeyConst key = a.keys[0];
+    const double xk = ((double)x - key.ox) / key.fx, yk = ((double)y - key.oy) / key.fy;
+    A1Result c;
+    double fail_d;
+    const int f = phase_a1(a, key, 0, xk, yk, 1, d, v, (double)a.W - 1., (double)a.H - 1., fail_d, c);
+    *out_flag = f == 1 ? TDK_FLAG_KEY_OUT_OF_RANGE : f;
+}
+
+// ---------------------------------------------------------------------------------------------
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t status, keys, pairs, key_ptrs, ref_ptrs, total_tile, cand_count, cand, total_queue;
-    size_t len_hist, counters_end, len_class, order, rec, total;
-    int64_t sub;   // keyframes per sub-batch of the sorted plan
+    size_t status, keys, pairs, key_ptrs, ref_ptrs, total_tile;
+    size_t counters, counters_end, cand, img32, total_queue, len_class, order, rec, total;
+    int64_t sub;   // keyframes per sub-batch of the queue plans
 };
 
-// The sorted plan's per-candidate arrays (137 bytes per pixel of a keyframe: worst case, every pixel
-// queued) are sized for a sub-batch of keyframes and reused by the sub-batches of a larger launch;
-// the kernels of successive sub-batches run in stream order.  Every sub-batch pays four kernel
-// tails, so bigger is faster (64 VGA keyframes: 24.8 / 22.3 / 20.8 / 20.0 us per keyframe with
-// sub-batches of 8 / 16 / 32 / 64).  tdk_update_depth_workspace_bytes() asks for min(P, SUB_BATCH)
-// keyframes' worth; launch() uses as many as the workspace it is given holds, down to one.
+// The queue plans' per-keyframe arrays (8 bytes per pixel for the queue and the f32 key image, plus
+// 133 bytes per pixel for the sorted plan's line records: worst case, every pixel queued) are sized
+// for a sub-batch of keyframes and reused by the sub-batches of a larger launch; the kernels of
+// successive sub-batches run in stream order.  Every sub-batch pays its kernels' tails, so bigger is
+// faster.  tdk_update_depth_workspace_bytes() asks for min(P, SUB_BATCH) keyframes' worth; launch()
+// uses as many as the workspace it is given holds, down to one.
 #ifndef TDK_SUB_BATCH
 #define TDK_SUB_BATCH 64
 #endif
 constexpr int64_t SUB_BATCH = TDK_SUB_BATCH;
+constexpr size_t COUNTER_WORDS = 2 + 2 * LEN_CLASSES;   // per sub-batch keyframe: queue length, max |image|, length histogram, cursor
 
-// total_tile: what the one-kernel plan needs; total_queue: plus the candidate queues of the
+// total_tile: what the one-kernel plan needs; total_queue: plus the queues and f32 key images of the
 // two-kernel plan; total: plus the line records of the sorted plan
 WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W, int64_t sub = SUB_BATCH)
 {
@@ -1113,16 +1230,16 @@ WsLayout ws_layout(int64_t P, int64_t R, int64_t H, int64_t W, int64_t sub = SUB
     l.total_tile = off;
     l.sub = P < sub ? P : sub;
     const size_t S = (size_t)l.sub, hw = (size_t)H * W;
-    // counters, contiguous so that pair_setup_kernel clears them in one sweep (the two-kernel plan
-    // only uses cand_count; 512 bytes per sub-batch keyframe are not worth a second layout)
-    l.cand_count = off; off = align_up(off + (size_t)P * sizeof(unsigned int), 256);
-    l.len_hist = off; off = align_up(off + S * 2 * LEN_CLASSES * sizeof(unsigned int), 256);   // hist, then cursor
+    // counters, contiguous so that one sweep clears them: [S] queue lengths, [S] max |image| bits,
+    // [S,64] length histogram, [S,64] cursor
+    l.counters = off; off = align_up(off + S * COUNTER_WORDS * sizeof(unsigned int), 256);
     l.counters_end = off;
-    l.cand = off; off = align_up(off + (size_t)P * H * W * sizeof(unsigned int), 256);
+    l.cand = off; off = align_up(off + S * hw * sizeof(unsigned int), 256);
+    l.img32 = off; off = align_up(off + S * hw * sizeof(float), 256);
     l.total_queue = off;
     l.len_class = off; off = align_up(off + S * hw, 256);
     l.order = off; off = align_up(off + S * hw * sizeof(unsigned int), 256);
-    // records: whole chunks of BLOCK slots (the sieve addresses the A1 results by chunk)
+    // records: whole chunks of BLOCK slots (lines_kernel writes them chunk by chunk)
     l.rec = off; off = align_up(off + S * align_up(hw, BLOCK) * REC_DOUBLE2 * sizeof(double2), 256);
     l.total = off;
     return l;
@@ -1144,7 +1261,14 @@ double sqrt_threshold(double m)
 }
 
 enum { PLAN_AUTO = -1, PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
-int g_plan = PLAN_AUTO;
+std::atomic<int> g_plan{PLAN_AUTO};
+
+// per-device one-time set-up (kernel attributes, SM count), safe against concurrent first calls
+struct DeviceInfo { std::once_flag once; int sm_count = 148; cudaError_t err = cudaSuccess; };
+DeviceInfo g_device_info[64];
+
+float float_down(double v) { float f = (float)v; return (double)f > v ? nextafterf(f, -INFINITY) : f; }
+float float_up(double v) { float f = (float)v; return (double)f < v ? nextafterf(f, INFINITY) : f; }
 
 // The sorted plan pays two more launches and a trip of the line records through the workspace; a
 // launch of a single VGA-sized keyframe is too small to earn that back (50 against 57 us).
@@ -1179,9 +1303,12 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         return TDK_ERR_INVALID;
     }
     WsLayout l = ws_layout(P, R, H, W);
-    if (plan == PLAN_SORTED)   // as many keyframes per sub-batch as the workspace holds
-        while (l.sub > 1 && workspace_bytes < l.total) l = ws_layout(P, R, H, W, l.sub - 1);
-    const size_t need = plan == PLAN_ONE_KERNEL ? l.total_tile : plan == PLAN_TWO_KERNELS ? l.total_queue : l.total;
+    auto need_of = [&](const WsLayout &w) {
+        return plan == PLAN_ONE_KERNEL ? w.total_tile : plan == PLAN_TWO_KERNELS ? w.total_queue : w.total;
+    };
+    if (plan != PLAN_ONE_KERNEL)   // as many keyframes per sub-batch as the workspace holds
+        while (l.sub > 1 && workspace_bytes < need_of(l)) l = ws_layout(P, R, H, W, l.sub - 1);
+    const size_t need = need_of(l);
     if (workspace_bytes < need) {
         tdk_set_error("tdk_update_depth: workspace %zu < required %zu", workspace_bytes, need);
         return TDK_ERR_WORKSPACE;
@@ -1193,7 +1320,26 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                       "keyframes per call)", (long long)P, nblocks);
         return TDK_ERR_INVALID;
     }
-    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)P);
+    int dev = 0;
+    TDK_CUDA(cudaGetDevice(&dev));
+    int sm_count = 148;
+    if (dev >= 0 && dev < 64) {
+        DeviceInfo &di = g_device_info[dev];
+        std::call_once(di.once, [&di, dev]() {
+            di.err = cudaDeviceGetAttribute(&di.sm_count, cudaDevAttrMultiProcessorCount, dev);
+            if (di.err == cudaSuccess)
+                di.err = cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)CTA_SMEM_BYTES);
+            if (di.err == cudaSuccess)
+                di.err = cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)CTA_SMEM_BYTES);
+        });
+        TDK_CUDA(di.err);
+        sm_count = di.sm_count;
+    } else {
+        tdk_set_error("tdk_update_depth: device ordinal %d not supported", dev);
+        return TDK_ERR_INVALID;
+    }
     char *ws = (char *)workspace;
     int *status = (int *)(ws + l.status);
     TdkKeyConst *keys = (TdkKeyConst *)(ws + l.keys);
@@ -1211,11 +1357,12 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         ref_ptrs = (const double *const *)(ws + l.ref_ptrs);
     }
     const int npairs = (int)(P * R);
+    const size_t counter_words = (size_t)l.sub * COUNTER_WORDS;
     pair_setup_kernel<<<(npairs + 127) / 128, 128, 0, stream>>>(
         key_imgs, key_ptrs, key_cams, T_wk, ref_imgs, ref_ptrs, ref_cams, T_wr, (int)P, (int)R,
         (size_t)H * W, keys, pairs, status,
-        plan == PLAN_ONE_KERNEL ? nullptr : (unsigned int *)(ws + l.cand_count),
-        plan == PLAN_ONE_KERNEL ? 0 : (int)((l.counters_end - l.cand_count) / sizeof(unsigned int)));
+        plan == PLAN_ONE_KERNEL ? nullptr : (unsigned int *)(ws + l.counters),
+        plan == PLAN_ONE_KERNEL ? 0 : (int)counter_words);
     TDK_CUDA(cudaGetLastError());
 
     UpdArgs a;
@@ -1227,66 +1374,99 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.vmax = 1. / (params[0] + TDK_EPS_INV);
     a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
     a.min_grad_sq = sqrt_threshold(a.min_grad);
-    a.p0 = 0; a.warp_budget = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr; a.len_hist = nullptr; a.len_cursor = nullptr;
+    a.p0 = 0; a.warp_budget = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr;
+    a.len_hist = nullptr; a.len_cursor = nullptr; a.cand = nullptr; a.cand_count = nullptr; a.img32 = nullptr; a.amax = nullptr;
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
-    static bool attr_set[64] = {};
-    static int sm_counts[64] = {};
-    int dev = 0;
-    TDK_CUDA(cudaGetDevice(&dev));
-    int sm_count = 148;
-    if (dev >= 0 && dev < 64) {
-        if (!sm_counts[dev]) TDK_CUDA(cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev));
-        sm_count = sm_counts[dev];
-    }
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        TDK_CUDA(cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)CTA_SMEM_BYTES));
-        TDK_CUDA(cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)CTA_SMEM_BYTES));
-        attr_set[dev] = true;
+    {   // constants of the certified sieve (phase_a0): coordinate error bound delta, margins, e / max |image|
+        const double two22 = 1. / 4194304., two24 = 1. / 16777216.;
+        const double delta = (2. * (double)CERT_HMAX + (double)(W > H ? W : H)) * two22;
+        const double dm = delta > 1e-3 ? delta : 1e-3;
+        a.cert_e = 2. * (4. * delta + 16. * two24) + two22;
+        a.cert_m = a.min_grad > 0. ? a.min_grad * (1. - 1e-5) : -1.;   // NaN -> -1
+        a.cert_lo = float_up(dm);
+        a.cert_xhi = float_down((double)W - 1. - dm);
+        a.cert_yhi = float_down((double)H - 1. - dm);
+        a.cert_out = float_down(-dm);
+        a.cert_xout = float_up((double)W - 1. + dm);
+        a.cert_yout = float_up((double)H - 1. + dm);
     }
     if (plan == PLAN_ONE_KERNEL) {
-        a.cand = nullptr; a.cand_count = nullptr;
-        update_depth_tile_kernel<<<grid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+        update_depth_tile_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)P), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
     } else {
-        a.cand_count = (unsigned int *)(ws + l.cand_count);
+        const size_t hw = (size_t)H * W;
+        unsigned int *counters = (unsigned int *)(ws + l.counters);
+        a.cand_count = counters;
+        a.amax = counters + l.sub;
+        a.len_hist = counters + 2 * l.sub;
+        a.len_cursor = a.len_hist + l.sub * LEN_CLASSES;
         a.cand = (unsigned int *)(ws + l.cand);
-        const unsigned qx = (unsigned)((tiles_x * tiles_y + 3) / 4);
-        if (plan == PLAN_TWO_KERNELS) {
-            update_depth_sieve_kernel<<<grid, BLOCK, 0, stream>>>(a);
-            TDK_CUDA(cudaGetLastError());
-            update_depth_search_kernel<<<dim3(qx, 1u, (unsigned)P), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
-        } else {
-            a.len_hist = (unsigned int *)(ws + l.len_hist);
-            a.len_cursor = a.len_hist + l.sub * LEN_CLASSES;
+        a.img32 = (const float *)(ws + l.img32);
+        if (plan == PLAN_SORTED) {
             a.len_class = (unsigned char *)(ws + l.len_class);
             a.order = (unsigned int *)(ws + l.order);
             a.rec = (double2 *)(ws + l.rec);
-            a.rec_stride = align_up((size_t)H * W, BLOCK);
-            for (int64_t p0 = 0; p0 < P; p0 += l.sub) {
-                const unsigned ns = (unsigned)(P - p0 < l.sub ? P - p0 : l.sub);
-                a.p0 = (int)p0;
-                if (p0 > 0)   // pair_setup_kernel cleared them for the first sub-batch
-                    TDK_CUDA(cudaMemsetAsync(a.len_hist, 0, (size_t)l.sub * 2 * LEN_CLASSES * sizeof(unsigned int), stream));
-                const dim3 sgrid(qx, 1u, ns);
+            a.rec_stride = align_up(hw, BLOCK);
+        }
+        const unsigned qx = (unsigned)((tiles_x * tiles_y + 3) / 4);
+        unsigned prep_x = (unsigned)((hw + 1023) / 1024);   // four pixels per thread
+        if (prep_x > 4096u) prep_x = 4096u;
+        for (int64_t p0 = 0; p0 < P; p0 += l.sub) {
+            const unsigned ns = (unsigned)(P - p0 < l.sub ? P - p0 : l.sub);
+            a.p0 = (int)p0;
+            if (p0 > 0)   // pair_setup_kernel cleared them for the first sub-batch
+                TDK_CUDA(cudaMemsetAsync(counters, 0, counter_words * sizeof(unsigned int), stream));
+            key_prep_kernel<<<dim3(prep_x, ns), 256, 0, stream>>>(keys, (int)p0, hw, (float *)(ws + l.img32),
+                                                                  counters + l.sub);
+            update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
+            if (plan == PLAN_TWO_KERNELS) {
+                update_depth_search_kernel<<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+            } else {
                 // 32 resident warps per SM at match_kernel's 64 registers.  Only launches of one or two
                 // keyframes leave warps idle; in a batch a sparse keyframe's spare warps belong to its
                 // neighbours, and whole-warp searches of short lines would cost throughput there.
                 a.warp_budget = ns <= 2 ? (int)((int64_t)sm_count * 32 / ns) : 0;
                 const unsigned mx = (unsigned)((a.warp_budget + MATCH_BLOCK / 32 - 1) / (MATCH_BLOCK / 32));
                 const unsigned mq = qx * (BLOCK / MATCH_BLOCK);
-                update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
-                update_depth_lines_kernel<<<sgrid, BLOCK, 0, stream>>>(a);
+                update_depth_lines_kernel<<<dim3(qx, 1u, ns), BLOCK, 0, stream>>>(a);
                 update_depth_order_kernel<<<dim3((qx + ORDER_ITEMS - 1) / ORDER_ITEMS, 1u, ns), BLOCK, 0, stream>>>(a);
                 update_depth_match_kernel<<<dim3(mx > mq ? mx : mq, 1u, ns), MATCH_BLOCK, 0, stream>>>(a);
-                TDK_CUDA(cudaGetLastError());
             }
+            TDK_CUDA(cudaGetLastError());
         }
     }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }
 
+}  // namespace
+
+// internal (capi.cu): the flag estimate_debug_ returns for a pixel outside the image; all pointers
+// but params are device pointers, scratch holds at least 1024 bytes
+int tdk_estimate_outside_dev(const double *key_cam, const double *T_wk, const double *ref_cam, const double *T_wr,
+                             const double *params, int64_t H, int64_t W, int64_t x, int64_t y, double prior_depth,
+                             double prior_variance, int *out_flag, void *scratch, cudaStream_t stream)
+{
+    char *ws = (char *)scratch;
+    int *status = (int *)ws;
+    TdkKeyConst *keys = (TdkKeyConst *)(ws + 256);
+    TdkPairConst *pairs = (TdkPairConst *)(ws + 512);
+    TDK_CUDA(cudaMemsetAsync(status, 0, TDK_ST_WORDS * sizeof(int), stream));
+    // the image pointers are stored, never followed: the range test fails first
+    pair_setup_kernel<<<1, 32, 0, stream>>>(key_cam, nullptr, key_cam, T_wk, key_cam, nullptr, ref_cam, T_wr, 1, 1,
+                                            (size_t)H * W, keys, pairs, status, nullptr, 0);
+    UpdArgs a = {};
+    a.keys = keys; a.pairs = pairs; a.status = status;
+    a.vmin = 1. / (params[1] + TDK_EPS_INV);
+    a.vmax = 1. / (params[0] + TDK_EPS_INV);
+    a.geo = params[2]; a.photo = params[3]; a.step = params[4]; a.min_grad = params[5];
+    a.min_grad_sq = sqrt_threshold(a.min_grad);
+    a.P = 1; a.R = 1; a.H = (int)H; a.W = (int)W;
+    estimate_outside_kernel<<<1, 1, 0, stream>>>(a, (long long)x, (long long)y, prior_depth, prior_variance, out_flag);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+namespace {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -1352,7 +1532,7 @@ int tdk_set_kernel_plan(int plan)
         tdk_set_error("tdk_set_kernel_plan: %d not in {-1,0,1,2}", plan);
         return TDK_ERR_INVALID;
     }
-    g_plan = plan;
+    g_plan.store(plan);
     return TDK_OK;
 }
 
@@ -1366,7 +1546,7 @@ int tdk_update_depth_dev(const double *key_imgs, const double *key_cams, const d
 {
     return launch(key_imgs, nullptr, key_cams, T_wk, ref_imgs, nullptr, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan, P, H, W), workspace, workspace_bytes,
+                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan.load(), P, H, W), workspace, workspace_bytes,
                   (cudaStream_t)stream);
 }
 
@@ -1381,7 +1561,7 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
 {
     return launch(nullptr, key_img_ptrs, key_cams, T_wk, nullptr, ref_img_ptrs, ref_cams, T_wr, age,
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
-                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan, P, H, W), workspace, workspace_bytes,
+                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan.load(), P, H, W), workspace, workspace_bytes,
                   (cudaStream_t)stream);
 }
 
@@ -1409,7 +1589,7 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
                                 int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
                                 int fuse_on_success, int wait_and_check, void *stream)
 {
-    if (P <= 0 || R <= 0 || P * R > TDK_STATIC_MAX_PAIRS ||
+    if (P <= 0 || R <= 0 || P > TDK_STATIC_MAX_PAIRS || R > TDK_STATIC_MAX_PAIRS || P * R > TDK_STATIC_MAX_PAIRS ||
         ws_layout(P, R, 1, 1).total_tile > (size_t)TDK_STATIC_SCRATCH_BYTES) {
         tdk_set_error("tdk_update_depth_static_dev: P*R = %lld x %lld exceeds the built-in scratch; this entry "
                       "point takes at most %d keyframe/reference pairs per call (use tdk_update_depth_dev "

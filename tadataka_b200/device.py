@@ -72,6 +72,8 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
     `out=(depth, variance, flag)` reuses preallocated output tensors.
     `fuse=True` fuses each successful measurement with its prior inside the kernel (Gaussian
     fusion in inverse depth, fusion.rs:3-11 / propagation.rs:27-34) instead of returning it raw.
+    `hist=True` returns a fresh [P,10] int64 count of every flag per keyframe; `hist=<tensor>`
+    ADDS the counts to that [P,10] int64 tensor (no allocation).
     """
     _require_cuda()
     _chk(key_imgs, "key_imgs", _F64)
@@ -102,7 +104,10 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
             _chk(ov, "out variance", _F64, (P, H, W))
             _chk(of, "out flag", torch.int64, (P, H, W))
         dbg = torch.empty((P, H, W), dtype=torch.int32, device=dev) if debug else None
-        hs = torch.zeros((P, 10), dtype=torch.int64, device=dev) if hist else None
+        if isinstance(hist, torch.Tensor):
+            hs = _chk(hist, "hist", torch.int64, (P, 10))
+        else:
+            hs = torch.zeros((P, 10), dtype=torch.int64, device=dev) if hist else None
         nbytes = _lib.update_depth_workspace_bytes(P, R, H, W)
         ws = workspace(nbytes, dev, "update_depth")
         rc = _lib.update_depth_dev(_ptr(key_imgs), _ptr(key_cams), _ptr(T_wk), _ptr(ref_imgs),
@@ -116,7 +121,7 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
     res = [od, ov, of]
     if debug:
         res.append(dbg)
-    if hist:
+    if hs is not None:
         res.append(hs)
     return tuple(res)
 

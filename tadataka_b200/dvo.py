@@ -48,24 +48,35 @@ def _dev(a):
     return torch.from_numpy(a).cuda()
 
 
-def tangent_so3(v):
-    return np.array([[0., -v[2], v[1]], [v[2], 0., -v[0]], [-v[1], v[0], 0.]])
+def _skew(w):
+    wx, wy, wz = float(w[0]), float(w[1]), float(w[2])
+    return np.array([[0., -wz, wy], [wz, 0., -wx], [-wy, wx, 0.]])
 
 
 def exp_se3(xi):
-    """4x4 matrix of the twist xi = (v, rotvec): tadataka/pose.py:44-46 + tadataka/se3.py:16-31."""
-    v, rotvec = xi[:3], xi[3:]
-    theta = np.linalg.norm(rotvec)
-    omega = np.zeros(3) if theta == 0 else rotvec / theta
-    K = tangent_so3(omega)
-    I = np.eye(3)
-    if theta < 1e-16:
-        V = I + K * theta / 2 + np.dot(K, K) * pow(theta, 2) / 6
+    """4x4 matrix of the twist xi = (v, w): rotation exp([w]x), translation V(w) v, the map
+    tadataka/pose.py:44-46 + tadataka/se3.py:16-31 compute.  Written on the un-normalised skew
+    matrix W = [w]x with the closed-form coefficients
+        a = sin(t)/t,  b = (1 - cos t)/t^2,  c = (t - sin t)/t^3,   t = |w|:
+        R = I + a W + b W^2,   V = I + b W + c W^2,
+    and their Taylor series below t = 1e-3 (where the closed forms cancel).  The reference switches to
+    its series only below t = 1e-16, so around t ~ 1e-8 its (1 - cos t)/t has cancelled to zero and it
+    is off by up to t/2 |v|; this form is not (agreement elsewhere: 1e-13)."""
+    xi = np.asarray(xi, dtype=np.float64)
+    W = _skew(xi[3:])
+    W2 = W @ W
+    t2 = float(xi[3] * xi[3] + xi[4] * xi[4] + xi[5] * xi[5])
+    if t2 < 1e-6:
+        a = 1. - t2 / 6. * (1. - t2 / 20.)
+        b = 0.5 - t2 / 24. * (1. - t2 / 30.)
+        c = 1. / 6. - t2 / 120. * (1. - t2 / 42.)
     else:
-        V = I + (1 - np.cos(theta)) / theta * K + (theta - np.sin(theta)) / theta * np.dot(K, K)
+        t = np.sqrt(t2)
+        st, ct = np.sin(t), np.cos(t)
+        a, b, c = st / t, (1. - ct) / t2, (t - st) / (t2 * t)
     T = np.eye(4)
-    T[:3, :3] = Rotation.from_rotvec(rotvec).as_matrix()
-    T[:3, 3] = np.dot(V, v)
+    T[:3, :3] += a * W + b * W2
+    T[:3, 3] = xi[:3] + b * (W @ xi[:3]) + c * (W2 @ xi[:3])
     return T
 
 

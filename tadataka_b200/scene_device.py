@@ -39,11 +39,15 @@ def render(world, T_wc, cams, H, W, device="cuda"):
     return image, depth
 
 
-def make_keyframes(seeds, R=8, H=480, W=640, cam=None, pset=scene.SET_S, yaw_deg=1.0, device="cuda"):
+def make_keyframes(seeds, R=8, H=480, W=640, cam=None, pset=scene.SET_S, yaw_deg=1.0, device="cuda",
+                   ages="blocks", per_item_rng=False):
     """One C2-style keyframe per seed, every one its own world: the batched arrays of
     scene.stack_keyframes as device tensors (same keys, plus params as a numpy array).  Poses follow
     scene.make_keyframe's seeded random walk; age blocks and priors come from a device generator
-    seeded with seeds[0], so the batch is reproducible but not equal to the numpy one."""
+    seeded with seeds[0], so the batch is reproducible but not equal to the numpy one.
+    ages="ones": every pixel uses the newest reference (C1 / C5 pairs).  per_item_rng=True: the
+    generator is re-seeded with each keyframe's own seed, so a keyframe does not depend on the batch
+    it is built in (what a sharded run needs to be comparable with a single-process one)."""
     dev = torch.device(device)
     cam = scene.CAM_VGA if cam is None else np.asarray(cam, dtype=np.float64)
     P = len(seeds)
@@ -66,14 +70,30 @@ def make_keyframes(seeds, R=8, H=480, W=640, cam=None, pset=scene.SET_S, yaw_deg
         out["T_wk"].append(torch.from_numpy(poses[0]).to(dev)); out["T_wr"].append(torch.from_numpy(poses[1:]).to(dev))
     b = {k: torch.stack(v).contiguous() for k, v in out.items()}
     g = torch.Generator(device=dev)
-    g.manual_seed(int(seeds[0]))
     by, bx = (H + 31) // 32, (W + 31) // 32
-    blocks = torch.randint(0, R + 1, (P, by, bx), generator=g, device=dev)
-    b["age"] = blocks.repeat_interleave(32, 1).repeat_interleave(32, 2)[:, :H, :W].contiguous().to(torch.int64)
+
+    def draw(n):
+        blocks = torch.randint(0, R + 1, (n, by, bx), generator=g, device=dev)
+        noise = torch.rand((n, H, W), generator=g, device=dev, dtype=torch.float64) * 0.2 - 0.1
+        logv = torch.rand((n, H, W), generator=g, device=dev, dtype=torch.float64) * 3.0 - 3.0
+        return blocks, noise, logv
+
+    if per_item_rng:
+        parts = []
+        for seed in seeds:
+            g.manual_seed(int(seed))
+            parts.append(draw(1))
+        blocks, noise, logv = (torch.cat([q[i] for q in parts]) for i in range(3))
+    else:
+        g.manual_seed(int(seeds[0]))
+        blocks, noise, logv = draw(P)
+    if ages == "ones":
+        b["age"] = torch.ones((P, H, W), dtype=torch.int64, device=dev)
+    else:
+        b["age"] = blocks.repeat_interleave(32, 1).repeat_interleave(32, 2)[:, :H, :W].contiguous().to(torch.int64)
     lo, hi = pset["params"][0], pset["params"][1]
-    noise = torch.rand((P, H, W), generator=g, device=dev, dtype=torch.float64) * 0.2 - 0.1
     b["prior_depth"] = torch.clamp(b["gt_depth"] * (1.0 + noise), lo * 1.01, hi * 0.99).contiguous()
-    b["prior_variance"] = (10.0 ** (torch.rand((P, H, W), generator=g, device=dev, dtype=torch.float64) * 3.0 - 3.0)).contiguous()
+    b["prior_variance"] = (10.0 ** logv).contiguous()
     camt = torch.from_numpy(cam).to(dev)
     b["key_cam"] = camt.repeat(P, 1).contiguous()
     b["ref_cams"] = camt.repeat(P, R, 1).contiguous()

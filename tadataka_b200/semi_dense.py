@@ -152,53 +152,71 @@ def estimate_debug_(u_key, prior_depth, prior_variance, keyframe, refframe, para
     return float(out[0]), float(out[1]), int(flag[0])
 
 
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
 def propagate(transform10, camera_params0, camera_params1, depth_map0, variance_map0,
               default_depth, default_variance, uncertaintity_bias):
     """-> (depth_map1, variance_map1).  `transform10` = T_1<-0 (src/py/semi_dense.rs:189-218;
-    the parameter really is spelt `uncertaintity_bias`)."""
+    the parameter really is spelt `uncertaintity_bias`).  One host-pointer C-ABI call
+    (tdk_propagate_host)."""
     transform10 = _need(transform10, "transform10", np.float64, 2)
     depth_map0 = _need(depth_map0, "depth_map0", np.float64, 2)
     variance_map0 = _need(variance_map0, "variance_map0", np.float64, 2)
     if transform10.shape != (4, 4) or depth_map0.shape != variance_map0.shape:
         raise ValueError("bad shapes")
-    d1, v1 = device.propagate(_cuda(transform10), _cuda(camera_vector(camera_params0)),
-                              _cuda(camera_vector(camera_params1)), _cuda(depth_map0),
-                              _cuda(variance_map0), default_depth, default_variance,
-                              uncertaintity_bias)
-    return d1.cpu().numpy(), v1.cpu().numpy()
+    device._require_cuda()
+    H, W = depth_map0.shape
+    cam0, cam1 = camera_vector(camera_params0), camera_vector(camera_params1)
+    d1, v1 = np.empty((H, W)), np.empty((H, W))
+    _lib.check(_lib.propagate_host(_p(transform10), _p(cam0), _p(cam1), _p(depth_map0), _p(variance_map0),
+                                   1, H, W, float(default_depth), float(default_variance),
+                                   float(uncertaintity_bias), _p(d1), _p(v1)))
+    return d1, v1
 
 
 def increment_age(age_map0, camera_params0, camera_params1, transform10, depth_map0):
-    """-> uint64 [H,W] (src/py/semi_dense.rs:35-51; note cameras come BEFORE the transform)."""
+    """-> uint64 [H,W] (src/py/semi_dense.rs:35-51; note cameras come BEFORE the transform).
+    One host-pointer C-ABI call (tdk_increment_age_host)."""
     age_map0 = _need(age_map0, "age_map0", np.uint64, 2)
     transform10 = _need(transform10, "transform10", np.float64, 2)
     depth_map0 = _need(depth_map0, "depth_map0", np.float64, 2)
     if transform10.shape != (4, 4) or depth_map0.shape != age_map0.shape:
         raise ValueError("bad shapes")
-    out = device.increment_age(_cuda(age_map0), _cuda(camera_vector(camera_params0)),
-                               _cuda(camera_vector(camera_params1)), _cuda(transform10),
-                               _cuda(depth_map0))
-    return out.cpu().numpy()
+    device._require_cuda()
+    H, W = age_map0.shape
+    cam0, cam1 = camera_vector(camera_params0), camera_vector(camera_params1)
+    out = np.empty((H, W), dtype=np.uint64)
+    _lib.check(_lib.increment_age_host(_p(age_map0), _p(cam0), _p(cam1), _p(transform10), _p(depth_map0),
+                                       1, H, W, _p(out)))
+    return out
 
 
 def fusion(mu1, mu2, var1, var2):
     """Elementwise Gaussian fusion -> (mu, var) (src/semi_dense/fusion.rs:13-42; argument order of
-    `fusion_arrays` and of examples/semi_dense_depth.py:41-42)."""
+    `fusion_arrays` and of examples/semi_dense_depth.py:41-42).  tdk_fusion_host."""
     arrs = [_need(a, n, np.float64, 2) for a, n in
             ((mu1, "mu1"), (mu2, "mu2"), (var1, "var1"), (var2, "var2"))]
     if any(a.shape != arrs[0].shape for a in arrs):
         raise ValueError("shapes differ")
-    mu, var = device.fusion(*[_cuda(a) for a in arrs])
-    return mu.cpu().numpy(), var.cpu().numpy()
+    device._require_cuda()
+    mu, var = np.empty(arrs[0].shape), np.empty(arrs[0].shape)
+    if mu.size:
+        _lib.check(_lib.fusion_host(*[_p(a) for a in arrs], None, mu.size, 0, _p(mu), _p(var)))
+    return mu, var
 
 
 def regularize(depth_map, variance_map, flag_map):
     """3x3 validity-weighted mean of inverse depth -> depth map (the signature of the reference's
-    commented-out binding, src/py/semi_dense.rs:220-233)."""
+    commented-out binding, src/py/semi_dense.rs:220-233).  tdk_regularize_host."""
     depth_map = _need(depth_map, "depth_map", np.float64, 2)
     variance_map = _need(variance_map, "variance_map", np.float64, 2)
     flag_map = _need(flag_map, "flag_map", np.int64, 2)
     if depth_map.shape != variance_map.shape or depth_map.shape != flag_map.shape:
         raise ValueError("shapes differ")
-    out = device.regularize(_cuda(depth_map), _cuda(variance_map), _cuda(flag_map))
-    return out.cpu().numpy()
+    device._require_cuda()
+    H, W = depth_map.shape
+    out = np.empty((H, W))
+    _lib.check(_lib.regularize_host(_p(depth_map), _p(variance_map), _p(flag_map), 1, H, W, _p(out)))
+    return out

@@ -147,7 +147,9 @@ def test_update_depth_workspace_sizes():
     least = [_lib.update_depth_workspace_bytes_min(P, R, H, W) for P in (1, 2, 64, 65, 300)]
     assert all(a >= b > 0 for a, b in zip(full, least)) and full[0] == least[0]
     assert full == sorted(full) and least == sorted(least)
-    # beyond 64 keyframes only the per-keyframe queue grows (4 bytes per pixel and small constants)
+    # beyond 64 keyframes (one sub-batch) only the per-keyframe constants grow: every per-pixel array
+    # belongs to the sub-batch and is reused
     per_kf = (full[4] - full[3]) / (300 - 65)
-    assert 4 * H * W <= per_kf < 5 * H * W
-    assert (full[2] - full[1]) / 62 > 137 * H * W
+    assert 0 < per_kf < 4096
+    # per sub-batch keyframe: queue 4 + f32 key image 4 + length class 1 + sort position 4 + record 128
+    assert 141 * H * W <= (full[2] - full[1]) / 62 < 142 * H * W

@@ -250,3 +250,58 @@ def test_drop_in_update_depth_and_estimate_debug():
     got = estimate_debug_(np.array(u), 200.0, 1.0, keyframe, refframe,
                           Params(60.0, 1000.0, 0.01, 0.01, 0.01, 0.2))
     assert got == want and got[2] == 0
+
+
+def test_host_pointer_companions_batched_through_the_c_abi():
+    """tdk_increment_age_host / tdk_propagate_host / tdk_fusion_host / tdk_regularize_host with P = 3
+    frames in one call, plain host pointers, against the oracle frame by frame."""
+    import ctypes as C
+    from tadataka_b200 import _lib
+    rng = np.random.default_rng(21)
+    P, H, W = 3, 60, 84
+    cam = np.array([80., 79., 41.5, 29.5])
+    cams = np.ascontiguousarray(np.tile(cam, (P, 1)))
+    T10 = np.stack([scene.pose(scene.rotation(0.01 * i, -0.02, 0.005), (0.3 * i, -0.1, 0.4 + 0.2 * i)) for i in range(P)])
+    depth0 = rng.uniform(4., 9., (P, H, W))
+    var0 = rng.uniform(0.01, 0.5, (P, H, W))
+    age0 = rng.integers(0, 5, (P, H, W)).astype(np.uint64)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p)
+
+    age1 = np.empty((P, H, W), dtype=np.uint64)
+    _lib.check(_lib.increment_age_host(p(age0), p(cams), p(cams), p(T10), p(depth0), P, H, W, p(age1)))
+    d1, v1 = np.empty((P, H, W)), np.empty((P, H, W))
+    _lib.check(_lib.propagate_host(p(T10), p(cams), p(cams), p(depth0), p(var0), P, H, W, 7.0, 50.0, 0.01, p(d1), p(v1)))
+    for i in range(P):
+        assert np.array_equal(age1[i], ora.increment_age(age0[i], cam, cam, T10[i], depth0[i]))
+        ed, ev = ora.propagate(T10[i], cam, cam, depth0[i], var0[i], 7.0, 50.0, 0.01)
+        assert np.array_equal(d1[i], ed) and np.array_equal(v1[i], ev)
+    flag = np.where(rng.random((P, H, W)) < 0.5, 0, -6).astype(np.int64)
+    mu, var = np.empty((P, H, W)), np.empty((P, H, W))
+    _lib.check(_lib.fusion_host(p(depth0), p(d1), p(var0), p(v1), p(flag), depth0.size, 0, p(mu), p(var)))
+    emu, evar = ora.fusion_arrays(depth0, d1, var0, v1)
+    assert np.array_equal(mu, np.where(flag == 0, emu, depth0)) and np.array_equal(var, np.where(flag == 0, evar, var0))
+    reg = np.empty((P, H, W))
+    _lib.check(_lib.regularize_host(p(depth0), p(var0), p(flag), P, H, W, p(reg)))
+    for i in range(P):
+        assert np.array_equal(reg[i], ora.regularize(depth0[i], var0[i], flag[i]))
+    assert _lib.regularize_host(None, p(var0), p(flag), P, H, W, p(reg)) == _lib.ERR_INVALID
+
+
+def test_estimate_debug_outside_the_image_returns_the_reference_flag():
+    """src/py/semi_dense.rs:126-155 runs estimate() for any u_key: a pixel outside the image ends at
+    KEY_OUT_OF_RANGE unless an earlier test (-7, -1, -8) fails first, and the prior is echoed."""
+    from rust_bindings.camera import CameraParameters
+    from rust_bindings.semi_dense import Frame, Params, estimate_debug_
+    it = scene.make_pair(77, H=48, W=64, cam=np.array([60., 60., 31.5, 23.5]))
+    cp = CameraParameters((60., 60.), (31.5, 23.5))
+    key, ref = Frame(cp, it["key_img"], it["T_wk"]), Frame(cp, it["ref_imgs"][0], it["T_wr"][0])
+    pr = it["params"]
+    params = Params(*pr)
+    for u in [(-1, 5), (64, 5), (10, -3), (10, 48), (500, 700)]:
+        for d, v in [(200.0, 0.1), (-5.0, 0.1), (1e-9, 1e-3)]:
+            want = ora.estimate_debug(u, d, v, it["key_img"], it["key_cam"], it["T_wk"], it["ref_imgs"][0],
+                                      it["ref_cams"][0], it["T_wr"][0], ora.make_params(*pr))
+            got = estimate_debug_(np.array(u, dtype=np.int64), d, v, key, ref, params)
+            assert got == want and got[0] == d and got[1] == v and got[2] in (-2, -7, -1, -8), (u, d, v, got, want)

@@ -144,3 +144,76 @@ def test_pruning_unused_reference_frames_changes_nothing_but_the_memory():
             lean._drop_unused_frames()
             assert lean.n_frames == 2 and keep.n_frames == 5
     assert lean.n_frames < keep.n_frames == n_frames
+
+
+def test_8bit_frames_are_converted_on_the_device_bit_for_bit():
+    """A mapper fed 8-bit gray / RGB / RGBA frames (converted by ingest_u8_kernel) holds exactly the
+    f64 images the host conversion gives -- v / 255 and the rgb2gray luma the reference's loaders
+    apply (tadataka/dataset/new_tsukuba.py:85-86), evaluated left to right -- and produces the same
+    maps as a mapper fed those f64 images."""
+    from rust_bindings.camera import CameraParameters
+    from tadataka_b200.mapper import SemiDenseMapper
+    H, W, n_frames = 96, 128, 5
+    cam = np.array([100.0, 100.0, 63.5, 47.5])
+    frames, cam, params = scene.make_sequence(3400, n_frames=n_frames, H=H, W=W, cam=cam)
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    rng = np.random.default_rng(3400)
+    depth0 = rng.uniform(params[0], params[1], (H, W))
+    gray8 = [np.round(f[0] * 255.0).astype(np.uint8) for f in frames]
+    rgba8 = []
+    for g in gray8:   # a colour frame whose channels differ, plus an alpha channel that must be ignored
+        c = np.stack([g, np.roll(g, 1, axis=1), 255 - g, rng.integers(0, 256, g.shape).astype(np.uint8)], axis=-1)
+        rgba8.append(np.ascontiguousarray(c))
+
+    def luma(c):
+        r, g, b = (c[..., k].astype(np.float64) / 255.0 for k in range(3))
+        return (r * 0.2125 + g * 0.7154) + b * 0.0721
+
+    for kind, raw, want in (("gray", gray8, [g.astype(np.float64) / 255.0 for g in gray8]),
+                            ("rgba", rgba8, [luma(c) for c in rgba8]),
+                            ("rgb", [np.ascontiguousarray(c[..., :3]) for c in rgba8], [luma(c) for c in rgba8])):
+        a = SemiDenseMapper(cp, raw[0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0, fuse=True)
+        b = SemiDenseMapper(cp, want[0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0, fuse=True)
+        for i in range(1, n_frames):
+            a.track(cp, raw[i], frames[i][1])
+            b.track(cp, want[i], frames[i][1])
+        a.sync()
+        held = a.reference_images().cpu().numpy()
+        assert held.shape == (n_frames, H, W)
+        for i in range(n_frames):
+            assert np.array_equal(held[i], want[i]), f"{kind} frame {i} differs from the host conversion"
+        for x, y in zip(a.maps(), b.maps()):
+            assert np.array_equal(x, y, equal_nan=True)
+    # the matmul form skimage uses agrees with the left-to-right luma to an ulp or two
+    from tests.golden_util import rgb2gray
+    assert np.abs(rgb2gray(rgba8[0][..., :3]) - luma(rgba8[0])).max() < 1e-15
+
+
+def test_mapper_ring_compacts_and_reports_a_full_ring():
+    """capacity 4 with pruning: the ring's window reaches the end of the arena and is moved to the
+    front without changing the maps; without pruning the fifth frame is refused."""
+    from rust_bindings.camera import CameraParameters
+    from tadataka_b200.mapper import SemiDenseMapper
+    H, W, n_frames = 64, 96, 10
+    cam = np.array([80.0, 80.0, 47.5, 31.5])
+    frames, cam, params = scene.make_sequence(3500, n_frames=n_frames, H=H, W=W, cam=cam)
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    depth0 = np.random.default_rng(3500).uniform(params[0], params[1], (H, W))
+    big = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0, capacity=32)
+    small = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0, prune=True,
+                            capacity=4)
+    for i in range(1, n_frames):
+        big.track(cp, frames[i][0], frames[i][1])
+        small.track(cp, frames[i][0], frames[i][1])
+        if i % 2 == 0:   # keep the map young so that old frames can go
+            for m in (big, small):
+                m.age = torch.clamp(m.age.to(torch.int64), max=1).to(torch.uint64)
+            small._drop_unused_frames()
+        for x, y in zip(big.maps(), small.maps()):
+            assert np.array_equal(x, y, equal_nan=True)
+    assert small.n_frames <= 4 and big.n_frames == n_frames
+    full = SemiDenseMapper(cp, frames[0][0], frames[0][1], params, 200.0, 100.0, 1e-6, depth_map=depth0, capacity=4)
+    for i in range(1, 4):
+        full.track(cp, frames[i][0], frames[i][1])
+    with pytest.raises(Exception, match="larger capacity"):
+        full.track(cp, frames[4][0], frames[4][1])

@@ -41,16 +41,21 @@ def _regular(t, params, fuse):
     return d, v, f, am
 
 
-def _static(t, params, fuse, wait_and_check=1):
+def _outputs(t):
+    P, H, W = t["key_img"].shape
+    return (torch.empty((P, H, W), dtype=torch.float64, device="cuda"),
+            torch.empty((P, H, W), dtype=torch.float64, device="cuda"),
+            torch.empty((P, H, W), dtype=torch.int64, device="cuda"),
+            torch.empty((P, H, W), dtype=torch.int32, device="cuda"))
+
+
+def _static(t, params, fuse, wait_and_check=1, out=None):
     """Call the new entry point the way a no-allocation caller does: its own input and output
     buffers, the stream, and nothing else."""
     from tadataka_b200 import _lib
     P, H, W = t["key_img"].shape
     R = t["ref_imgs"].shape[1]
-    d = torch.empty((P, H, W), dtype=torch.float64, device="cuda")
-    v = torch.empty((P, H, W), dtype=torch.float64, device="cuda")
-    f = torch.empty((P, H, W), dtype=torch.int64, device="cuda")
-    am = torch.empty((P, H, W), dtype=torch.int32, device="cuda")
+    d, v, f, am = out if out is not None else _outputs(t)
     pa = np.ascontiguousarray(params, dtype=np.float64)
     rc = _lib.update_depth_static_dev(
         *(C.c_void_p(t[k].data_ptr()) for k in NAMES), pa.ctypes.data_as(C.c_void_p), P, R, H, W,
@@ -78,6 +83,34 @@ def test_two_calls_in_a_row_match_the_regular_entry_point():
     assert (want1[2] == 0).sum() > 0 and (want2[2] == 0).sum() > 0
     assert _same(got1, want1), "first call differs from tdk_update_depth_dev"
     assert _same(got2, want2), "second call differs from tdk_update_depth_dev"
+
+
+def test_matches_the_oracle_and_leaves_device_memory_alone():
+    """The entry point against the CPU oracle directly (not only against the other CUDA entry
+    point), and the property it exists for: once the caller's own buffers are there, calls of
+    different shapes change nothing in the amount of free device memory."""
+    import oracle as ora
+    from tadataka_b200 import _lib
+    batches = [_batch(960, P=3, R=4), _batch(970, P=1, R=8, H=80, W=200), _batch(980, P=8, R=8, H=48, W=64)]
+    ins = [_device_inputs(b) for b in batches]
+    outs = [_outputs(t) for t in ins]
+    rc, _ = _static(ins[0], batches[0]["params"], fuse=False, out=outs[0])   # first call: address look-up
+    assert rc == _lib.OK, _lib.last_error()
+    torch.cuda.synchronize()
+    free_before, _total = torch.cuda.mem_get_info()
+    for b, t, o in zip(batches, ins, outs):
+        rc, _ = _static(t, b["params"], fuse=False, out=o)
+        assert rc == _lib.OK, _lib.last_error()
+    torch.cuda.synchronize()
+    free_after, _total = torch.cuda.mem_get_info()
+    assert free_after == free_before, "tdk_update_depth_static_dev changed the free device memory"
+    for b, (d, v, f, am) in zip(batches, outs):
+        od, ov, of, oam, _ = ora.update_depth_batch(*(b[k] for k in NAMES), ora.make_params(*b["params"]),
+                                                    debug=True)
+        assert np.array_equal(f.cpu().numpy(), of) and np.array_equal(am.cpu().numpy(), oam)
+        assert np.array_equal(d.cpu().numpy(), od, equal_nan=True)
+        assert np.array_equal(v.cpu().numpy(), ov, equal_nan=True)
+        assert (of == 0).sum() > 0
 
 
 def test_an_error_left_by_one_call_does_not_leak_into_the_next():
@@ -110,4 +143,8 @@ def test_batches_beyond_the_built_in_scratch_are_refused():
     msg = _lib.last_error().decode()
     assert "at most 64" in msg and "tdk_update_depth_dev" in msg
     assert _lib.STATIC_MAX_PAIRS == 64
+    # sizes whose product overflows 64 bits are refused by the per-factor test, not by the product
+    rc = _lib.update_depth_static_dev(z, z, z, z, z, z, z, z, z, pa.ctypes.data_as(C.c_void_p), 2 ** 62, 4,
+                                      H, W, z, z, z, None, None, 0, 1, None)
+    assert rc == _lib.ERR_INVALID
     del fake
