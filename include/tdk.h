@@ -363,7 +363,11 @@ int tdk_selftest_shared_division_dev(int64_t n, uint64_t seed, uint64_t *mismatc
  *   the SAME pixel, as the reference computes it (:90).  weight_mode: 0 none, 1 `weights` map
  *   (:71-72), 2 Huber with k = weight_param (robust/weights.py:38-43), 3 Student-t with
  *   variance = weight_param and nu (robust/weights.py:4-20; find the variance with
- *   tdk_dvo_student_t_dev).  Tukey weights need a median and are not provided.
+ *   tdk_dvo_student_t_dev), 4 Tukey biweight with weight_param = c * MAD of the residuals
+ *   (robust/weights.py:23-35, beta = 4.6851; find the scale with tdk_dvo_tukey_scale_dev).
+ * tdk_dvo_tukey_scale_dev: out = 1 device double = c_mad * median(|r - median(r)|) over the same pixels
+ *   (np.median semantics: the two middle values are averaged for an even count); a one-CTA radix
+ *   select over the gathered residuals.  workspace: tdk_dvo_tukey_workspace_bytes(H, W).
  * tdk_dvo_student_t_dev: out = {sum of r^2 (nu+1)/(nu + r^2/variance), count} over the same pixels:
  *   one step of the variance fixed point of compute_weights_student_t.
  * tdk_dvo_photometric_error_dev: out = {sum (I0 - I1(warp))^2, count} over the pixels whose warped
@@ -381,6 +385,11 @@ int tdk_dvo_student_t_dev(const double *I0, const double *D0, const double *I1, 
 int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const double *I1,
                                   const double *cam0, const double *cam1, const double *T10,
                                   int64_t H, int64_t W, double *out, void *stream);
+size_t tdk_dvo_tukey_workspace_bytes(int64_t H, int64_t W);
+int tdk_dvo_tukey_scale_dev(const double *I0, const double *D0, const double *I1, double c_mad,
+                            const double *cam0, const double *cam1, const double *T10, int64_t H,
+                            int64_t W, double *out, void *workspace, size_t workspace_bytes,
+                            void *stream);
 
 #ifdef __cplusplus
 }

@@ -94,6 +94,9 @@ dvo_student_t_dev = _sig("tdk_dvo_student_t_dev", C.c_int, P, P, P, D, D, P, P, 
 dvo_photometric_error_dev = _sig("tdk_dvo_photometric_error_dev", C.c_int, P, P, P, P, P, P, I64, I64, P,
                                  P)
 
+dvo_tukey_workspace_bytes = _sig("tdk_dvo_tukey_workspace_bytes", SZ, I64, I64)
+dvo_tukey_scale_dev = _sig("tdk_dvo_tukey_scale_dev", C.c_int, P, P, P, D, P, P, P, I64, I64, P, P, SZ, P)
+
 # every symbol include/tdk.h declares (tests check the header against this list and the .so)
 EXPORTS = [
     "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
@@ -110,6 +113,7 @@ EXPORTS = [
     "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
     "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
     "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",
+    "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev",
 ]
 
 

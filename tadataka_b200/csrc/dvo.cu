@@ -79,17 +79,25 @@ __device__ __forceinline__ void block_accumulate(double (&acc)[N], double *s_acc
     if (threadIdx.x < N) atomicAdd(&out[threadIdx.x], s_acc[threadIdx.x]);
 }
 
-enum { W_NONE = 0, W_ARRAY = 1, W_HUBER = 2, W_STUDENT_T = 3 };
+enum { W_NONE = 0, W_ARRAY = 1, W_HUBER = 2, W_STUDENT_T = 3, W_TUKEY = 4 };
+constexpr double TUKEY_BETA = 4.6851;   // weights.py:34
 
 // effective weight of the normal equations.  The reference scales rows by sqrt(weights)
 // (math.py:45-49), i.e. the normal equations carry `weights` itself:
 //   huber      weights.py:38-43  w = 1 if |r| <= k else k / |r|
 //   student-t  weights.py:4-20   the function returns sqrt((nu+1) / (nu + r^2 / variance))
+//   tukey      weights.py:23-35  (1 - (u / beta)^2)^2 for |u| <= beta else 0, u = r / (c * MAD)
 __device__ __forceinline__ double row_weight(int mode, double param, double nu, double r, const double *wmap, size_t i)
 {
     if (mode == W_ARRAY) return wmap[i];
     if (mode == W_HUBER) { const double a = fabs(r); return a > param ? param / a : 1.; }
     if (mode == W_STUDENT_T) return sqrt((nu + 1.) / (nu + (r * r) / param));
+    if (mode == W_TUKEY) {   // weights.py:23-35: param = c * MAD (tdk_dvo_tukey_scale_dev)
+        const double u = r / param;
+        if (!(fabs(u) <= TUKEY_BETA)) return 0.;
+        const double q = u / TUKEY_BETA, t = 1. - q * q;
+        return t * t;
+    }
     return 1.;
 }
 
@@ -185,6 +193,95 @@ __global__ void __launch_bounds__(TPB) dvo_photometric_error_kernel(const double
     block_accumulate<2>(acc, s_acc, out);
 }
 
+// ---- Tukey scale: c * median(|r - median(r)|) over the residuals of the usable pixels
+// (weights.py:29-35).  residual_compact_kernel gathers them (order is irrelevant to a median);
+// median_select_kernel, one CTA, finds the middle element(s) by an 8-pass radix select over
+// order-preserving 64-bit keys and averages the two middle ones for an even count, as np.median does.
+__global__ void __launch_bounds__(TPB) residual_compact_kernel(const double *__restrict__ I0, const double *__restrict__ D0,
+                                                               const double *__restrict__ I1, const DvoConst c, int H,
+                                                               int W, double *__restrict__ out, unsigned int *count)
+{
+    const int hw = H * W;
+    for (int i0 = blockIdx.x * TPB; i0 < hw; i0 += gridDim.x * TPB) {
+        const int i = i0 + threadIdx.x;
+        bool ok = false;
+        double r = 0.;
+        if (i < hw) {
+            const int y = i / W, x = i - y * W;
+            double u, v, px, py, pz;
+            warp_pixel(c, x, y, D0[i], u, v, px, py, pz);
+            ok = tdk::in_range(u, v, (double)W - 1., (double)H - 1.) && pz > 0.;
+            r = I0[i] - I1[i];
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (m) {
+            const int lane = threadIdx.x & 31;
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(count, (unsigned)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (ok) out[base + __popc(m & ((1u << lane) - 1u))] = r;
+        }
+    }
+}
+
+__device__ __forceinline__ unsigned long long order_key(double v)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double key_value(unsigned long long k)
+{
+    const unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+    return __longlong_as_double((long long)b);
+}
+
+// values[0..n): *result = median (np.median semantics).  If abs_dev != 0 the median is taken of
+// |values[i] - *centre| instead and *result = scale * that.  One CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) median_select_kernel(const double *__restrict__ values, const unsigned int *count,
+                                                             int abs_dev, const double *centre, double scale,
+                                                             double *result)
+{
+    __shared__ unsigned int s_hist[256];
+    __shared__ unsigned long long s_prefix;
+    __shared__ unsigned int s_rank;
+    __shared__ double s_found[2];
+    const unsigned int n = *count;
+    if (n == 0) { if (threadIdx.x == 0) *result = __longlong_as_double(0x7ff8000000000000ll); return; }
+    const double ctr = abs_dev ? *centre : 0.;
+    const unsigned int ranks[2] = {(n - 1) / 2, n / 2};
+    for (int which = 0; which < 2; which++) {
+        if (which == 1 && ranks[1] == ranks[0]) { if (threadIdx.x == 0) s_found[1] = s_found[0]; break; }
+        if (threadIdx.x == 0) { s_prefix = 0ull; s_rank = ranks[which]; }
+        for (int pass = 0; pass < 8; pass++) {
+            const int shift = 56 - 8 * pass;
+            if (threadIdx.x < 256) s_hist[threadIdx.x] = 0;
+            __syncthreads();
+            const unsigned long long prefix = s_prefix;
+            const unsigned long long mask = pass == 0 ? 0ull : ~0ull << (shift + 8);
+            for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) {
+                const double v = abs_dev ? fabs(values[i] - ctr) : values[i];
+                const unsigned long long k = order_key(v);
+                if ((k & mask) == prefix) atomicAdd(&s_hist[(unsigned)(k >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                unsigned int r = s_rank, b = 0;
+                while (b < 255 && r >= s_hist[b]) { r -= s_hist[b]; b++; }
+                s_rank = r;
+                s_prefix = prefix | ((unsigned long long)b << shift);
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) s_found[which] = key_value(s_prefix);
+        __syncthreads();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double med = ranks[0] == ranks[1] ? s_found[0] : (s_found[0] + s_found[1]) / 2.;
+        *result = abs_dev ? scale * med : med;
+    }
+}
+
 DvoConst make_const(const double *cam0, const double *cam1, const double *T10)
 {
     DvoConst c;
@@ -230,7 +327,7 @@ int tdk_dvo_normal_equations_dev(const double *I0, const double *D0, const doubl
 {
     int rc = check_image("tdk_dvo_normal_equations_dev", H, W, I0 && D0 && I1 && GX1 && GY1 && cam0 && cam1 && T10 && out);
     if (rc != TDK_OK) return rc;
-    if (weight_mode < W_NONE || weight_mode > W_STUDENT_T || (weight_mode == W_ARRAY && !weights)) {
+    if (weight_mode < W_NONE || weight_mode > W_TUKEY || (weight_mode == W_ARRAY && !weights)) {
         tdk_set_error("tdk_dvo_normal_equations_dev: bad weight mode %d", weight_mode);
         return TDK_ERR_INVALID;
     }
@@ -253,6 +350,35 @@ int tdk_dvo_student_t_dev(const double *I0, const double *D0, const double *I1, 
     TDK_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), st));
     dvo_student_t_kernel<<<reduce_grid(H * W), TPB, 0, st>>>(I0, D0, I1, variance, nu, make_const(cam0, cam1, T10),
                                                             (int)H, (int)W, out);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+size_t tdk_dvo_tukey_workspace_bytes(int64_t H, int64_t W)
+{
+    if (H <= 0 || W <= 0) return 0;
+    return 256 + (size_t)H * W * sizeof(double);
+}
+
+int tdk_dvo_tukey_scale_dev(const double *I0, const double *D0, const double *I1, double c_mad, const double *cam0,
+                            const double *cam1, const double *T10, int64_t H, int64_t W, double *out,
+                            void *workspace, size_t workspace_bytes, void *stream)
+{
+    int rc = check_image("tdk_dvo_tukey_scale_dev", H, W, I0 && D0 && I1 && cam0 && cam1 && T10 && out && workspace);
+    if (rc != TDK_OK) return rc;
+    if (workspace_bytes < tdk_dvo_tukey_workspace_bytes(H, W)) {
+        tdk_set_error("tdk_dvo_tukey_scale_dev: workspace too small");
+        return TDK_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned int *count = (unsigned int *)workspace;
+    double *median = (double *)((char *)workspace + 64);
+    double *values = (double *)((char *)workspace + 256);
+    TDK_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
+    residual_compact_kernel<<<reduce_grid(H * W), TPB, 0, st>>>(I0, D0, I1, make_const(cam0, cam1, T10), (int)H, (int)W,
+                                                               values, count);
+    median_select_kernel<<<1, 1024, 0, st>>>(values, count, 0, nullptr, 1., median);
+    median_select_kernel<<<1, 1024, 0, st>>>(values, count, 1, median, c_mad, out);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

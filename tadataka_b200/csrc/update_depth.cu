@@ -524,11 +524,24 @@ __device__ __forceinline__ double line_sample(const LineGeom &g, int i, double s
 __device__ __forceinline__ double window_error(double s0, double s1, double s2, double s3, double s4,
                                                double k0, double k1, double k2, double k3, double k4)
 {
+#ifdef TDK_GATE_SEARCH
+    // Experiment (not shipped; DESIGN.md "gate-tolerance build"): with both windows normalised the
+    // error is 2 - 2 cos, so the argmin is the argmax of <s, k^> / |s|; an approximate reciprocal
+    // square root (one Newton step, ~2^-40) instead of sqrt + five IEEE divisions.
+    const double n2 = s0 * s0 + s1 * s1 + s2 * s2 + s3 * s3 + s4 * s4;
+    const double dot = s0 * k0 + s1 * k1 + s2 * k2 + s3 * k3 + s4 * k4;
+    if (!(n2 > 0.)) return n2 == 0. ? 0.5 : n2;   // empty window; NaN stays NaN
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(n2));
+    y = y * __fma_rn(-0.5 * n2, y * y, 1.5);
+    return 1. - dot * y;
+#else
     const double wn = sqrt(s0 * s0 + s1 * s1 + s2 * s2 + s3 * s3 + s4 * s4);
     double w0 = s0, w1 = s1, w2 = s2, w3 = s3, w4 = s4;
     if (wn != 0.) tdk::div5(w0, w1, w2, w3, w4, wn);
     const double d0 = w0 - k0, d1 = w1 - k1, d2 = w2 - k2, d3 = w3 - k3, d4 = w4 - k4;
     return d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3 + d4 * d4;
+#endif
 }
 
 // Phase C in registers for the pixel (sx, sy) whose search returned `arg` (= argmin + 2).  Returns the

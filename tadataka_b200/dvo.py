@@ -31,6 +31,7 @@ from .camera import camera_vector
 _F64 = torch.float64
 HUBER_K = 1.345       # tadataka/robust/weights.py:38
 STUDENT_NU = 5.0      # tadataka/robust/weights.py:4
+TUKEY_C = 1.4826      # tadataka/robust/weights.py:32 (beta = 4.6851 lives in csrc/dvo.cu)
 STUDENT_ITERS = 10
 
 
@@ -127,6 +128,17 @@ class _Level:
             variance = s / n
         return variance
 
+    def _tukey_scale(self, T10):
+        """c * MAD of the residuals of the usable pixels (robust/weights.py:29-35), found on the device."""
+        nbytes = _lib.dvo_tukey_workspace_bytes(self.H, self.W)
+        ws = device.workspace(nbytes, self.I0.device, "dvo_tukey")
+        _lib.check(_lib.dvo_tukey_scale_dev(
+            device._ptr(self.I0), device._ptr(self.D0), device._ptr(self.I1), TUKEY_C, _vp(self.cam0),
+            _vp(self.cam1), _vp(T10), self.H, self.W, device._ptr(self.acc), device._ptr(ws), ws.numel(),
+            device._stream()))
+        scale = float(self.acc[0].item())
+        return None if np.isnan(scale) else scale
+
     def normal_equations(self, T10, weights):
         """-> (A [6,6], b [6], n_used) of calc_pose_update, or None if no pixel is usable."""
         T10 = np.ascontiguousarray(T10, dtype=np.float64)
@@ -141,7 +153,9 @@ class _Level:
                 if param is None:
                     return None
             elif weights == "tukey":
-                raise NotImplementedError("tukey weights need a device median; use 'huber' or 'student-t'")
+                mode, param = 4, self._tukey_scale(T10)
+                if param is None:
+                    return None
             else:
                 raise ValueError(f"No such weights '{weights}'")
         else:

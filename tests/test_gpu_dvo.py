@@ -57,7 +57,7 @@ def test_image_gradient_is_numpy_gradient():
         assert np.array_equal(gx.cpu().numpy(), DX) and np.array_equal(gy.cpu().numpy(), DY)
 
 
-@pytest.mark.parametrize("weights", [None, "array", "huber", "student-t"])
+@pytest.mark.parametrize("weights", [None, "array", "huber", "student-t", "tukey"])
 def test_normal_equations_and_error_match_oracle(weights):
     from tadataka_b200 import dvo
     cam, I0, D0, I1, T10_true = _pair()
@@ -74,7 +74,26 @@ def test_normal_equations_and_error_match_oracle(weights):
         assert abs(e - oe) <= RTOL_SUMS * oe
 
 
-@pytest.mark.parametrize("weights", [None, "huber", "student-t"])
+def test_tukey_scale_is_the_exact_median_absolute_deviation():
+    """tdk_dvo_tukey_scale_dev (radix-select medians on the device) == c * np.median(|r - np.median(r)|)
+    of the usable pixels' residuals, bit for bit, for odd and even counts
+    (tadataka/robust/weights.py:29-35)."""
+    from tadataka_b200 import dvo
+    for seed, H, W in ((9100, 60, 80), (9101, 61, 83), (9102, 96, 128)):
+        cam, I0, D0, I1, T10_true = _pair(seed=seed, H=H, W=W)
+        level = dvo._Level(cam, cam, I0, D0, I1)
+        for T10 in (np.eye(4), T10_true):
+            us0 = odvo.image_coordinates(I0.shape)
+            P0 = ora.inv_project_vecs(odvo.normalize(cam, us0.astype(np.float64)), D0.flatten())
+            P1 = np.dot(T10[:3, :3], P0.T).T + T10[:3, 3]
+            us1 = odvo.unnormalize(cam, ora.project_vecs(P1))
+            mask = odvo.is_in_image_range(us1, I0.shape) & (P1[:, 2] > 0)
+            r = (I0 - I1).flatten()[mask]
+            want = 1.4826 * np.median(np.abs(r - np.median(r)))
+            assert level._tukey_scale(np.ascontiguousarray(T10)) == want, (seed, r.size)
+
+
+@pytest.mark.parametrize("weights", [None, "huber", "student-t", "tukey"])
 def test_single_level_estimator_follows_the_oracle(weights):
     from tadataka_b200 import dvo
     cam, I0, D0, I1, T10_true = _pair()
@@ -99,7 +118,7 @@ def test_pyramid_estimator_and_error_cases():
     est = dvo.PoseChangeEstimator(cp, cp, n_coarse_to_fine=4, max_iter=20)
     e_id = odvo.photometric_error(np.eye(4), cam, cam, I0, D0, I1)
     e_true = odvo.photometric_error(T10_true, cam, cam, I0, D0, I1)
-    for weights in (None, np.ones(I0.shape), "huber", "student-t"):
+    for weights in (None, np.ones(I0.shape), "huber", "student-t", "tukey"):
         T = est(I0, D0, I1, weights)
         e = odvo.photometric_error(T, cam, cam, I0, D0, I1)
         assert e < e_id, weights
