@@ -161,6 +161,14 @@ int tdk_update_depth_static_dev(const double *key_imgs, const double *key_cams, 
  * total, 2 for larger ones.  Results do not depend on it. */
 int tdk_set_kernel_plan(int plan);
 
+/* No counterpart in the reference: its search returns an integer sample index
+ * (src/semi_dense/intensities.rs:11-36, used at semi_dense.rs:147-148).  on != 0: every later
+ * update_depth call fits a parabola through the errors of the best window and its two neighbours
+ * and triangulates from the sample position at its minimum (offset within half a sample) instead
+ * of the sample itself -- depth and variance then differ from the reference's; flags and dbg_argmin
+ * do not change except through the final range check.  Default 0 (off): results are the reference's. */
+int tdk_set_subpixel_refinement(int on);
+
 /* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,
  * checks the status.  Host buffers may be pageable or pinned. */
 int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const double *T_wk,

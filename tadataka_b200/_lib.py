@@ -36,6 +36,7 @@ def _sig(name, restype, *argtypes):
 last_error = _sig("tdk_last_error", C.c_char_p)
 version = _sig("tdk_version", C.c_char_p)
 set_kernel_plan = _sig("tdk_set_kernel_plan", C.c_int, C.c_int)
+set_subpixel_refinement = _sig("tdk_set_subpixel_refinement", C.c_int, C.c_int)
 DEFAULT_PLAN = -1  # automatic: sorted line records (2) except for single small keyframes (0); update_depth.cu
 update_depth_workspace_bytes = _sig("tdk_update_depth_workspace_bytes", SZ, I64, I64, I64, I64)
 update_depth_workspace_bytes_min = _sig("tdk_update_depth_workspace_bytes_min", SZ, I64, I64, I64, I64)
@@ -113,7 +114,7 @@ EXPORTS = [
     "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
     "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
     "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",
-    "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev",
+    "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev", "tdk_set_subpixel_refinement",
 ]
 
 

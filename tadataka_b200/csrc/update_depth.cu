@@ -72,6 +72,7 @@ struct UpdArgs {
     float cert_lo, cert_xhi, cert_yhi;      // a coordinate in [lo, hi] is inside the image for certain
     float cert_out, cert_xout, cert_yout;   // a coordinate < out or > [xy]out is outside for certain
     int P, R, H, W, tiles_x, tiles_y, fuse;
+    int subpix;                 // opt-in sub-sample refinement of the search result (not in the reference)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -544,17 +545,38 @@ __device__ __forceinline__ double window_error(double s0, double s1, double s2, 
 #endif
 }
 
+// Opt-in sub-sample refinement (north star step 3; the reference has none: intensities.rs:11-36
+// returns an integer index, so this is OFF unless tdk_set_subpixel_refinement(1) was called and
+// results then no longer match the reference).  A parabola through the errors of the best window
+// and its two neighbours; returns the offset of its minimum in samples, within [-0.5, 0.5], or 0
+// when the best window sits at an end of the line or the three errors do not bracket a minimum.
+__device__ __forceinline__ double subpixel_offset(const LineGeom &g, int n, int best, double step, int W, int H,
+                                                  double k0, double k1, double k2, double k3, double k4)
+{
+    if (best < 1 || best + 1 > n - 5) return 0.;
+    double s[7];
+#pragma unroll
+    for (int j = 0; j < 7; j++) s[j] = line_sample(g, best - 1 + j, step, W, H);
+    const double em = window_error(s[0], s[1], s[2], s[3], s[4], k0, k1, k2, k3, k4);
+    const double e0 = window_error(s[1], s[2], s[3], s[4], s[5], k0, k1, k2, k3, k4);
+    const double ep = window_error(s[2], s[3], s[4], s[5], s[6], k0, k1, k2, k3, k4);
+    const double den = (em - e0) + (ep - e0);
+    if (!(den > 0.) || !(em >= e0) || !(ep >= e0)) return 0.;
+    const double off = 0.5 * (em - ep) / den;
+    return off < -0.5 ? -0.5 : off > 0.5 ? 0.5 : off;
+}
+
 // Phase C in registers for the pixel (sx, sy) whose search returned `arg` (= argmin + 2).  Returns the
 // final flag; on SUCCESS nd / nv hold the new (or fused) depth and variance.  pv = prior variance.
 __device__ __forceinline__ int phase_c_core(const UpdArgs &a, const TdkKeyConst &key,
                                             const TdkPairConst *__restrict__ pc, int arg, int sx, int sy, double xk,
                                             double yk, double xminx, double xminy, double ux, double uy,
                                             double rdx, double rdy, double g, double kstep, double pv,
-                                            size_t map_base, double &nd, double &nv)
+                                            size_t map_base, double &nd, double &nv, double sub = 0.)
 {
     const int W = a.W, H = a.H;
     const double *__restrict__ T = pc->T;
-    const double s = (double)arg * a.step;
+    const double s = ((double)arg + sub) * a.step;   // sub = 0 unless the opt-in refinement ran: x + 0. == x
     const double xr = xminx + s * ux;
     const double yr = xminy + s * uy;
 
@@ -621,13 +643,18 @@ __device__ __forceinline__ int phase_c_core(const UpdArgs &a, const TdkKeyConst 
 }
 
 // Phase C for a live queue slot q.
+template <bool SUBPIX>
 __device__ __forceinline__ int phase_c(const UpdArgs &a, const CtaQueue &Q, const TdkKeyConst &key, int p, int q,
                                        size_t map_base, double &nd, double &nv)
 {
     const TdkPairConst *__restrict__ pc = a.pairs + (size_t)p * a.R + Q.ref[q];
+    double sub = 0.;
+    if (SUBPIX)
+        sub = subpixel_offset(line_geom(a, Q, p, q), Q.n[q], Q.arg[q] - 2, a.step, a.W, a.H, Q.k[0][q], Q.k[1][q],
+                              Q.k[2][q], Q.k[3][q], Q.k[4][q]);
     return phase_c_core(a, key, pc, Q.arg[q], Q.px[q] & 0xffff, Q.px[q] >> 16, Q.xk[q], Q.yk[q], Q.xminx[q],
                         Q.xminy[q], Q.ux[q], Q.uy[q], Q.rdx[q], Q.rdy[q], Q.g[q], Q.kstep[q], Q.v[q], map_base,
-                        nd, nv);
+                        nd, nv, sub);
 }
 
 // Search of ONE line by a full warp: lane i takes sample base+i, windows come from shfl_down, the
@@ -736,6 +763,7 @@ __device__ __forceinline__ void phase_b(const UpdArgs &a, CtaQueue &Q, int p, in
 // One-kernel plan: a CTA owns a 64x4 tile, compacts its own candidates and runs every phase.
 // Needs no global queue (this is what tdk_update_depth_static_dev runs), but only the tile's own
 // ~5-15 % of candidates populate phases A2/B/C.
+template <bool SUBPIX>
 __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(const UpdArgs a)
 {
     extern __shared__ __align__(16) unsigned char s_dyn[];
@@ -800,7 +828,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
     // ---- phases B and C
     phase_b(a, Q, p, nq, [&](int q) {
         double nd, nv;
-        const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
+        const int f = phase_c<SUBPIX>(a, Q, key, p, q, map_base, nd, nv);
         const int owner = Q.owner[q];
         if (f == TDK_FLAG_SUCCESS) { s_depth[owner] = nd; s_var[owner] = nv; }
         s_flag[owner] = (signed char)f;
@@ -911,6 +939,7 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     }
 }
 
+template <bool SUBPIX>
 __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(const UpdArgs a)
 {
     extern __shared__ __align__(16) unsigned char s_dyn[];
@@ -957,7 +986,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_search_kernel(co
         // ---- phases B and C, then the scattered store, all by the thread that searched the line
         phase_b(a, Q, p, nq, [&](int q) {
             double nd, nv;
-            const int f = phase_c(a, Q, key, p, q, map_base, nd, nv);
+            const int f = phase_c<SUBPIX>(a, Q, key, p, q, map_base, nd, nv);
             const size_t at = map_base + (size_t)(Q.px[q] >> 16) * W + (Q.px[q] & 0xffff);
             if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
             else a.out_f[at] = (long long)f;
@@ -1118,6 +1147,7 @@ __global__ void __launch_bounds__(BLOCK) update_depth_order_kernel(const UpdArgs
 #define TDK_MATCH_BLOCK 128   // four warps per CTA: finer-grained scheduling of the longest-first item order (18.1 vs 18.3 us per keyframe)
 #endif
 constexpr int MATCH_BLOCK = TDK_MATCH_BLOCK;
+template <bool SUBPIX>
 __global__ void __launch_bounds__(MATCH_BLOCK, MATCH_MIN_CTAS * BLOCK / MATCH_BLOCK) update_depth_match_kernel(const UpdArgs a)
 {
     __shared__ unsigned int s_hist[10], s_start[LEN_CLASSES];
@@ -1180,8 +1210,9 @@ __global__ void __launch_bounds__(MATCH_BLOCK, MATCH_MIN_CTAS * BLOCK / MATCH_BL
         const double xk = ((double)sx - key.ox) / key.fx, yk = ((double)sy - key.oy) / key.fy;
         const double2 r5 = r[5], r6 = r[6];
         double nd, nv;
+        const double sub = SUBPIX ? subpixel_offset(g, t.n, arg - 2, a.step, W, H, k0, k1, k2, k3, k4) : 0.;
         const int f = phase_c_core(a, key, pc, arg, sx, sy, xk, yk, r2.y, r3.x, r3.y, r4.x, r4.y, r5.x, r5.y,
-                                   r6.x, r6.y, map_base, nd, nv);
+                                   r6.x, r6.y, map_base, nd, nv, sub);
         const size_t at = map_base + (size_t)sy * W + sx;
         if (f == TDK_FLAG_SUCCESS) { a.out_d[at] = nd; a.out_v[at] = nv; }
         else a.out_f[at] = (long long)f;
@@ -1275,6 +1306,7 @@ double sqrt_threshold(double m)
 
 enum { PLAN_AUTO = -1, PLAN_TWO_KERNELS = 0, PLAN_ONE_KERNEL = 1, PLAN_SORTED = 2 };
 std::atomic<int> g_plan{PLAN_AUTO};
+std::atomic<int> g_subpixel{0};
 
 // per-device one-time set-up (kernel attributes, SM count), safe against concurrent first calls
 struct DeviceInfo { std::once_flag once; int sm_count = 148; cudaError_t err = cudaSuccess; };
@@ -1341,10 +1373,16 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         std::call_once(di.once, [&di, dev]() {
             di.err = cudaDeviceGetAttribute(&di.sm_count, cudaDevAttrMultiProcessorCount, dev);
             if (di.err == cudaSuccess)
-                di.err = cudaFuncSetAttribute(update_depth_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                di.err = cudaFuncSetAttribute(update_depth_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)CTA_SMEM_BYTES);
             if (di.err == cudaSuccess)
-                di.err = cudaFuncSetAttribute(update_depth_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                di.err = cudaFuncSetAttribute(update_depth_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)CTA_SMEM_BYTES);
+            if (di.err == cudaSuccess)
+                di.err = cudaFuncSetAttribute(update_depth_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)CTA_SMEM_BYTES);
+            if (di.err == cudaSuccess)
+                di.err = cudaFuncSetAttribute(update_depth_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)CTA_SMEM_BYTES);
         });
         TDK_CUDA(di.err);
@@ -1390,6 +1428,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     a.p0 = 0; a.warp_budget = 0; a.rec_stride = 0; a.rec = nullptr; a.len_class = nullptr; a.order = nullptr;
     a.len_hist = nullptr; a.len_cursor = nullptr; a.cand = nullptr; a.cand_count = nullptr; a.img32 = nullptr; a.amax = nullptr;
     a.P = (int)P; a.R = (int)R; a.H = (int)H; a.W = (int)W; a.tiles_x = tiles_x; a.tiles_y = tiles_y; a.fuse = fuse ? 1 : 0;
+    a.subpix = g_subpixel.load();
     {   // constants of the certified sieve (phase_a0): coordinate error bound delta, margins, e / max |image|
         const double two22 = 1. / 4194304., two24 = 1. / 16777216.;
         const double delta = (2. * (double)CERT_HMAX + (double)(W > H ? W : H)) * two22;
@@ -1404,7 +1443,9 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
         a.cert_yout = float_up((double)H - 1. + dm);
     }
     if (plan == PLAN_ONE_KERNEL) {
-        update_depth_tile_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)P), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+        const dim3 tgrid((unsigned)tiles_x, (unsigned)tiles_y, (unsigned)P);
+        if (a.subpix) update_depth_tile_kernel<true><<<tgrid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+        else update_depth_tile_kernel<false><<<tgrid, BLOCK, CTA_SMEM_BYTES, stream>>>(a);
     } else {
         const size_t hw = (size_t)H * W;
         unsigned int *counters = (unsigned int *)(ws + l.counters);
@@ -1432,7 +1473,8 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                                                                   counters + l.sub);
             update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
             if (plan == PLAN_TWO_KERNELS) {
-                update_depth_search_kernel<<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+                if (a.subpix) update_depth_search_kernel<true><<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
+                else update_depth_search_kernel<false><<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
             } else {
                 // 32 resident warps per SM at match_kernel's 64 registers.  Only launches of one or two
                 // keyframes leave warps idle; in a batch a sparse keyframe's spare warps belong to its
@@ -1442,7 +1484,9 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 const unsigned mq = qx * (BLOCK / MATCH_BLOCK);
                 update_depth_lines_kernel<<<dim3(qx, 1u, ns), BLOCK, 0, stream>>>(a);
                 update_depth_order_kernel<<<dim3((qx + ORDER_ITEMS - 1) / ORDER_ITEMS, 1u, ns), BLOCK, 0, stream>>>(a);
-                update_depth_match_kernel<<<dim3(mx > mq ? mx : mq, 1u, ns), MATCH_BLOCK, 0, stream>>>(a);
+                const dim3 mgrid(mx > mq ? mx : mq, 1u, ns);
+                if (a.subpix) update_depth_match_kernel<true><<<mgrid, MATCH_BLOCK, 0, stream>>>(a);
+                else update_depth_match_kernel<false><<<mgrid, MATCH_BLOCK, 0, stream>>>(a);
             }
             TDK_CUDA(cudaGetLastError());
         }
@@ -1546,6 +1590,12 @@ int tdk_set_kernel_plan(int plan)
         return TDK_ERR_INVALID;
     }
     g_plan.store(plan);
+    return TDK_OK;
+}
+
+int tdk_set_subpixel_refinement(int on)
+{
+    g_subpixel.store(on ? 1 : 0);
     return TDK_OK;
 }
 

@@ -460,3 +460,35 @@ def test_update_depth_replays_from_a_cuda_graph():
         assert int((out[2] == 0).sum()) > 20
         # new priors in the same buffers: the graph must pick them up
         t["prior_variance"].mul_(0.5)
+
+
+def test_subpixel_refinement_is_off_by_default_and_lowers_the_depth_error():
+    """north star step 3 (opt-in; the reference has none).  Default: nothing changes.
+    Switched on: flags and search indices stay, depths of the successful pixels move, and against
+    the synthetic scene's exact depth their median error shrinks in every plan."""
+    from tadataka_b200 import _lib, device
+    it = scene.make_pair(1234, H=240, W=320, cam=np.array([260.0, 259.0, 159.5, 119.5]))
+    b = scene.stack_keyframes([it, scene.make_pair(1235, H=240, W=320, cam=np.array([260.0, 259.0, 159.5, 119.5]))])
+    names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth", "prior_variance"]
+    t = _dev(b)
+    gt = b["gt_depth"]
+    try:
+        for plan in (2, 0, 1):
+            _lib.check(_lib.set_kernel_plan(plan))
+            d0, v0, f0, a0 = device.update_depth(*(t[k] for k in names), b["params"], debug=True)
+            _lib.check(_lib.set_subpixel_refinement(1))
+            d1, v1, f1, a1 = device.update_depth(*(t[k] for k in names), b["params"], debug=True)
+            _lib.check(_lib.set_subpixel_refinement(0))
+            d2, v2, f2, a2 = device.update_depth(*(t[k] for k in names), b["params"], debug=True)
+            assert torch.equal(d0, d2) and torch.equal(v0, v2) and torch.equal(f0, f2) and torch.equal(a0, a2)
+            d0, d1, f0, f1 = d0.cpu().numpy(), d1.cpu().numpy(), f0.cpu().numpy(), f1.cpu().numpy()
+            assert np.array_equal(a0.cpu().numpy(), a1.cpu().numpy())
+            both = (f0 == 0) & (f1 == 0)
+            assert both.sum() > 1000 and (f0 != f1).mean() < 1e-3
+            assert (d0[both] != d1[both]).mean() > 0.5
+            e0, e1 = np.abs(d0[both] - gt[both]), np.abs(d1[both] - gt[both])
+            assert np.median(e1) < np.median(e0), (plan, np.median(e0), np.median(e1))
+            assert e1.mean() < e0.mean(), (plan, e0.mean(), e1.mean())
+    finally:
+        _lib.set_subpixel_refinement(0)
+        _lib.set_kernel_plan(_lib.DEFAULT_PLAN)
