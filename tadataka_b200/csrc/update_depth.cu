@@ -863,11 +863,22 @@ __global__ void __launch_bounds__(256) key_prep_kernel(const TdkKeyConst *__rest
     const double *__restrict__ src = keys[pl + p0].img;
     float *__restrict__ dst = img32 + (size_t)pl * hw;
     float m = 0.f;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hw; i += (size_t)gridDim.x * blockDim.x) {
-        const double v = __ldg(src + i);
-        dst[i] = (float)v;
-        const float av = __double2float_ru(fabs(v));
-        m = av == av ? fmaxf(m, av) : INFINITY;   // a NaN in the image switches the cheap path off
+    constexpr int PER = 8;   // independent loads in flight per thread
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < hw; i0 += stride * PER) {
+        double v[PER];
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const size_t i = i0 + k * stride;
+            v[k] = i < hw ? __ldg(src + i) : 0.;
+        }
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const size_t i = i0 + k * stride;
+            if (i < hw) dst[i] = (float)v[k];
+            const float av = __double2float_ru(fabs(v[k]));
+            m = av == av ? fmaxf(m, av) : INFINITY;   // a NaN in the image switches the cheap path off
+        }
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
@@ -875,9 +886,16 @@ __global__ void __launch_bounds__(256) key_prep_kernel(const TdkKeyConst *__rest
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(amax + pl, __float_as_uint(m));
 }
 
+#ifndef TDK_SIEVE_PPT
+#define TDK_SIEVE_PPT 2
+#endif
+constexpr int SIEVE_PPT = TDK_SIEVE_PPT;              // pixels per thread: rows ly, ly + 4, ... of a 64 x (4 PPT) tile
+constexpr int SIEVE_TILE_H = TILE_H * SIEVE_PPT;
+static_assert(TILE_W + SIEVE_TILE_H + 1 <= BLOCK, "the table set-up needs one thread per column, row and threshold");
+
 __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kernel(const UpdArgs a)
 {
-    __shared__ double s_xk[TILE_W], s_yk[TILE_H];
+    __shared__ double s_xk[TILE_W], s_yk[SIEVE_TILE_H];
     __shared__ unsigned int s_hist[10];
     __shared__ float s_thr2;
 
@@ -889,49 +907,64 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     const TdkKeyConst key = a.keys[p];
 
     const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
-    const int x = tx * TILE_W + lx, y = ty * TILE_H + ly;
-    const bool valid = x < W && y < H;
-    const size_t pix = map_base + (size_t)y * W + x;
-    // the three map loads go out first, so their DRAM latency overlaps the table set-up below
-    uint64_t age = 0;
-    double d = 0., v = 0.;
-    if (valid) { age = a.age[pix]; d = a.prior_d[pix]; v = a.prior_v[pix]; }
+    const int x = tx * TILE_W + lx, y0 = ty * SIEVE_TILE_H + ly;
+    // every map load of the thread's pixels goes out first: their DRAM latency overlaps the table
+    // set-up below and each other
+    uint64_t age[SIEVE_PPT];
+    double d[SIEVE_PPT], v[SIEVE_PPT];
+#pragma unroll
+    for (int k = 0; k < SIEVE_PPT; k++) {
+        const int y = y0 + k * TILE_H;
+        age[k] = 0; d[k] = 0.; v[k] = 0.;
+        if (x < W && y < H) {
+            const size_t pix = map_base + (size_t)y * W + x;
+            age[k] = a.age[pix]; d[k] = a.prior_d[pix]; v[k] = a.prior_v[pix];
+        }
+    }
 
     if (tid < 10) s_hist[tid] = 0;
     // camera.rs:55-57: x_key depends on the column (row) only -- one division per column (row) of
     // the tile instead of two per pixel
     if (tid < TILE_W) s_xk[tid] = ((double)(tx * TILE_W + tid) - key.ox) / key.fx;
-    else if (tid < TILE_W + TILE_H) s_yk[tid - TILE_W] = ((double)(ty * TILE_H + tid - TILE_W) - key.oy) / key.fy;
-    else if (tid == TILE_W + TILE_H) s_thr2 = cert_threshold(a, a.amax[pl]);
+    else if (tid < TILE_W + SIEVE_TILE_H) s_yk[tid - TILE_W] = ((double)(ty * SIEVE_TILE_H + tid - TILE_W) - key.oy) / key.fy;
+    else if (tid == TILE_W + SIEVE_TILE_H) s_thr2 = cert_threshold(a, a.amax[pl]);
     __syncthreads();
 
-    int flag = TDK_FLAG_NOT_PROCESSED;
-    if (valid) {
-        double out_d = d;
-        if (age != 0) {
-            if (age > (uint64_t)a.R) {
-                atomicExch(&a.status[TDK_ST_AGE], 1);
-            } else {
-                flag = phase_a0(a, key, a.img32 + (size_t)pl * hw, p, x, y, s_xk[lx], s_yk[ly], age, d, v, s_thr2,
-                                out_d);
+    const float *__restrict__ img32 = a.img32 + (size_t)pl * hw;
+    const float thr2 = s_thr2;
+    const double xk = s_xk[lx];
+    const int lane = tid & 31;
+#pragma unroll
+    for (int k = 0; k < SIEVE_PPT; k++) {
+        const int y = y0 + k * TILE_H;
+        const bool valid = x < W && y < H;
+        int flag = TDK_FLAG_NOT_PROCESSED;
+        if (valid) {
+            const size_t pix = map_base + (size_t)y * W + x;
+            double out_d = d[k];
+            if (age[k] != 0) {
+                if (age[k] > (uint64_t)a.R) {
+                    atomicExch(&a.status[TDK_ST_AGE], 1);
+                } else {
+                    flag = phase_a0(a, key, img32, p, x, y, xk, s_yk[ly + k * TILE_H], age[k], d[k], v[k], thr2, out_d);
+                }
             }
+            // undecided pixels get the values a failed estimate keeps; the later kernels overwrite the
+            // flag if the exact path fails them and all three values on success
+            a.out_d[pix] = out_d;
+            a.out_v[pix] = v[k];
+            a.out_f[pix] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
+            if (a.dbg) a.dbg[pix] = -1;
+            if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
         }
-        // undecided pixels get the values a failed estimate keeps; the later kernels overwrite the
-        // flag if the exact path fails them and all three values on success
-        a.out_d[pix] = out_d;
-        a.out_v[pix] = v;
-        a.out_f[pix] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
-        if (a.dbg) a.dbg[pix] = -1;
-        if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
-    }
-    // append this warp's undecided pixels to the keyframe's queue: one global atomic per warp, no CTA barrier
-    const unsigned cmask = __ballot_sync(0xffffffffu, flag == 1);
-    if (cmask) {
-        const int lane = tid & 31;
-        unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(a.cand_count + pl, (unsigned int)__popc(cmask));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (flag == 1) a.cand[(size_t)pl * hw + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
+        // append this warp's undecided pixels to the keyframe's queue: one global atomic per warp, no CTA barrier
+        const unsigned cmask = __ballot_sync(0xffffffffu, flag == 1);
+        if (cmask) {
+            unsigned int base = 0;
+            if (lane == 0) base = atomicAdd(a.cand_count + pl, (unsigned int)__popc(cmask));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (flag == 1) a.cand[(size_t)pl * hw + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
+        }
     }
     if (a.hist) {
         __syncthreads();
@@ -1462,7 +1495,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
             a.rec_stride = align_up(hw, BLOCK);
         }
         const unsigned qx = (unsigned)((tiles_x * tiles_y + 3) / 4);
-        unsigned prep_x = (unsigned)((hw + 1023) / 1024);   // four pixels per thread
+        unsigned prep_x = (unsigned)((hw + 2047) / 2048);   // eight pixels per thread
         if (prep_x > 4096u) prep_x = 4096u;
         for (int64_t p0 = 0; p0 < P; p0 += l.sub) {
             const unsigned ns = (unsigned)(P - p0 < l.sub ? P - p0 : l.sub);
@@ -1471,7 +1504,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
                 TDK_CUDA(cudaMemsetAsync(counters, 0, counter_words * sizeof(unsigned int), stream));
             key_prep_kernel<<<dim3(prep_x, ns), 256, 0, stream>>>(keys, (int)p0, hw, (float *)(ws + l.img32),
                                                                   counters + l.sub);
-            update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)tiles_y, ns), BLOCK, 0, stream>>>(a);
+            update_depth_sieve_kernel<<<dim3((unsigned)tiles_x, (unsigned)((H + SIEVE_TILE_H - 1) / SIEVE_TILE_H), ns), BLOCK, 0, stream>>>(a);
             if (plan == PLAN_TWO_KERNELS) {
                 if (a.subpix) update_depth_search_kernel<true><<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);
                 else update_depth_search_kernel<false><<<dim3(qx, 1u, ns), BLOCK, CTA_SMEM_BYTES, stream>>>(a);

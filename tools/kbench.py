@@ -21,10 +21,20 @@ ap.add_argument("--iters", type=int, default=20)
 ap.add_argument("--plans", default="0,1")
 ap.add_argument("--c4", action="store_true", help="720p TUM-scale pairs instead of C2")
 ap.add_argument("--no-parity", action="store_true")
+ap.add_argument("--device-scenes", action="store_true", help="every keyframe its own world from the CUDA ray-caster (fast set-up; implies --no-parity)")
 ap.add_argument("--smooth", action="store_true", help="prior variance constant per 32x32 block, prior depth = ground truth with a smooth 3 %% bias (what a propagated map looks like) instead of per-pixel noise")
 args = ap.parse_args()
 
-if args.c4:
+if args.device_scenes:
+    from tadataka_b200 import scene_device
+    args.no_parity = True
+    if args.c4:
+        tt = scene_device.make_keyframes([4000 + i for i in range(args.keyframes)], R=1, H=720, W=1280, cam=scene.CAM_720P,
+                                         pset=scene.SET_T, ages="ones", per_item_rng=True)
+    else:
+        tt = scene_device.make_keyframes([2000 + i for i in range(args.keyframes)], R=8)
+    b = {"params": tt["params"], "key_img": tt["key_img"]}
+elif args.c4:
     b = scene.stack_keyframes([scene.make_pair(4000 + i, H=720, W=1280, cam=scene.CAM_720P, pset=scene.SET_T)
                                for i in range(args.keyframes)])
 else:
@@ -40,7 +50,7 @@ if args.smooth:
     lo, hi = b["params"][0], b["params"][1]
     b["prior_depth"] = np.ascontiguousarray(np.clip(b["gt_depth"] * bias, lo * 1.01, hi * 0.99))
 names = ["key_img", "key_cam", "T_wk", "ref_imgs", "ref_cams", "T_wr", "age", "prior_depth", "prior_variance"]
-t = {k: torch.from_numpy(b[k]).cuda() for k in names}
+t = {k: tt[k] for k in names} if args.device_scenes else {k: torch.from_numpy(b[k]).cuda() for k in names}
 if not args.no_parity:
     t0 = time.time()
     od, ov, of, oam, onn = ora.update_depth_batch(*(b[k] for k in names), ora.make_params(*b["params"]),
