@@ -179,6 +179,19 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
                           int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
                           int fuse_on_success);
 
+/* Host-pointer form with the frames passed by pointer: key_img_ptrs [P] and ref_img_ptrs [P*R] are
+ * HOST arrays of HOST image pointers ([H,W] f64 each).  An image named more than once -- the
+ * reference frames of the reference's own loop, where every new keyframe is matched against the
+ * frames before it (examples/semi_dense_vo.py:196-203; src/py/semi_dense.rs:157-187 clones every
+ * reference per call) -- is uploaded once per call.  Everything else as tdk_update_depth_host. */
+int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double *key_cams,
+                                 const double *T_wk, const double *const *ref_img_ptrs,
+                                 const double *ref_cams, const double *T_wr, const uint64_t *age,
+                                 const double *prior_depth, const double *prior_variance,
+                                 const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
+                                 double *out_depth, double *out_variance, int64_t *out_flag,
+                                 int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success);
+
 /* Replaces rust_bindings.semi_dense.estimate_debug_ (src/py/semi_dense.rs:126-155): one pixel,
  * host pointers, returns the prior on failure.  u_key is (x, y).  out = {depth, variance},
  * *out_flag the flag, dbg (optional, 1 value) = argmin+2 of the search, or -1. */

@@ -50,6 +50,8 @@ STATIC_MAX_PAIRS = 64
 update_depth_status = _sig("tdk_update_depth_status", C.c_int, P, P)
 update_depth_host = _sig("tdk_update_depth_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
                          I64, I64, P, P, P, P, P, C.c_int)
+update_depth_frames_host = _sig("tdk_update_depth_frames_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
+                                I64, I64, P, P, P, P, P, C.c_int)
 estimate_debug_host = _sig("tdk_estimate_debug_host", C.c_int, P, D, D, P, P, P, P, P, P, P, I64,
                            I64, P, P, P)
 fusion_dev = _sig("tdk_fusion_dev", C.c_int, P, P, P, P, P, I64, C.c_int, P, P, P)
@@ -114,7 +116,7 @@ EXPORTS = [
     "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
     "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
     "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",
-    "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev", "tdk_set_subpixel_refinement",
+    "tdk_update_depth_frames_host", "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev", "tdk_set_subpixel_refinement",
 ]
 
 

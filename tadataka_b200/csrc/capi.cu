@@ -7,6 +7,8 @@
 #include <string.h>
 
 #include <mutex>
+#include <unordered_map>
+#include <vector>
 
 #include "tdk_common.cuh"
 
@@ -39,7 +41,32 @@ struct Arena {
     bool streams_ready = false;
     int *status_host = nullptr;      // pinned, grow-only: the status words of every chunk of a call
     size_t status_words = 0;
+    std::vector<cudaEvent_t> events; // grow-only pool (tdk_update_depth_frames_host: "images of chunk c are up")
 };
+
+int status_host_get(Arena *ar, int64_t nchunks)
+{
+    if (ar->status_words < (size_t)(TDK_ST_WORDS * nchunks)) {
+        if (ar->status_host) { TDK_CUDA(cudaFreeHost(ar->status_host)); ar->status_host = nullptr; ar->status_words = 0; }
+        const size_t want = (size_t)TDK_ST_WORDS * (nchunks < 64 ? 64 : nchunks);
+        TDK_CUDA(cudaMallocHost((void **)&ar->status_host, sizeof(int) * want));
+        ar->status_words = want;
+    }
+    return TDK_OK;
+}
+
+int status_report(const int (*st)[TDK_ST_WORDS], int64_t nchunks)
+{
+    for (int64_t c = 0; c < nchunks; c++) {
+        if (st[c][TDK_ST_SINGULAR]) { tdk_set_error("a reference pose T_wr is singular"); return TDK_ERR_SINGULAR; }
+        if (st[c][TDK_ST_AGE]) { tdk_set_error("Age exceeds the refframe size"); return TDK_ERR_AGE; }
+        if (st[c][TDK_ST_SEARCH_LEN]) {
+            tdk_set_error("an epipolar search line has more than %d samples; increase ref_step_size", TDK_MAX_SEARCH_SAMPLES);
+            return TDK_ERR_SEARCH_LEN;
+        }
+    }
+    return TDK_OK;
+}
 Arena g_arena[MAX_DEV];
 std::mutex g_mutex[MAX_DEV];   // one per device: host-pointer calls on different GPUs do not serialise
 
@@ -209,6 +236,139 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
             }
         }
     }
+    return rc;
+}
+
+// update_depth from host memory with frames passed by POINTER: an image that several keyframes
+// name -- the reference frames of the reference's own loop, examples/semi_dense_vo.py:196-203, where
+// every keyframe is matched against the frames before it -- crosses PCIe once.  Chunks of keyframes
+// rotate over three streams; the images a chunk needs that are not on the device yet go up on the
+// first stream just before it, so image upload, kernels and the copy back of earlier chunks overlap.
+int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double *key_cams, const double *T_wk,
+                                 const double *const *ref_img_ptrs, const double *ref_cams, const double *T_wr,
+                                 const uint64_t *age, const double *prior_depth, const double *prior_variance,
+                                 const double *params, int64_t P, int64_t R, int64_t H, int64_t W, double *out_depth,
+                                 double *out_variance, int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
+                                 int fuse_on_success)
+{
+    if (!key_img_ptrs || !ref_img_ptrs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
+        !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
+        tdk_set_error("tdk_update_depth_frames_host: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    if (P <= 0 || R <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_update_depth_frames_host: bad sizes");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0;
+    int rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t hw = (size_t)H * W;
+    // distinct images, in the order the keyframes need them
+    std::unordered_map<const double *, int64_t> index;
+    std::vector<const double *> unique;
+    auto slot_of = [&](const double *img) {
+        auto it = index.find(img);
+        if (it != index.end()) return it->second;
+        const int64_t k = (int64_t)unique.size();
+        index.emplace(img, k);
+        unique.push_back(img);
+        return k;
+    };
+    std::vector<int64_t> key_slot((size_t)P), ref_slot((size_t)(P * R));
+    for (int64_t p = 0; p < P; p++) {
+        if (!key_img_ptrs[p]) { tdk_set_error("tdk_update_depth_frames_host: null image pointer"); return TDK_ERR_INVALID; }
+        key_slot[p] = slot_of(key_img_ptrs[p]);
+        for (int64_t r = 0; r < R; r++) {
+            if (!ref_img_ptrs[p * R + r]) { tdk_set_error("tdk_update_depth_frames_host: null image pointer"); return TDK_ERR_INVALID; }
+            ref_slot[p * R + r] = slot_of(ref_img_ptrs[p * R + r]);
+        }
+    }
+    const int64_t U = (int64_t)unique.size();
+    // chunk = keyframes whose maps (3 in, 3 out) make up ~96 MB
+    int64_t C = (int64_t)((96u << 20) / (6 * hw * 8));
+    if (C < 1) C = 1;
+    if (C > P) C = P;
+    const int64_t nchunks = (P + C - 1) / C;
+    const int nslots = (int)(nchunks < NSTREAM ? nchunks : NSTREAM);
+    struct FSlot { double *cams, *T_wk, *ref_cams, *T_wr, *pd, *pv, *od, *ov; uint64_t *age; int64_t *of; int32_t *dbg; uint64_t *hist; void *ws; size_t ws_bytes; };
+    auto carve = [&](char *base, size_t off, FSlot *f) {
+        auto take = [&](size_t bytes) { char *q = base ? base + off : nullptr; off += up256(bytes); return q; };
+        FSlot t;
+        t.cams = (double *)take(C * 4 * 8); t.T_wk = (double *)take(C * 16 * 8);
+        t.ref_cams = (double *)take(C * R * 4 * 8); t.T_wr = (double *)take(C * R * 16 * 8);
+        t.age = (uint64_t *)take(C * hw * 8); t.pd = (double *)take(C * hw * 8); t.pv = (double *)take(C * hw * 8);
+        t.od = (double *)take(C * hw * 8); t.ov = (double *)take(C * hw * 8); t.of = (int64_t *)take(C * hw * 8);
+        t.dbg = dbg_argmin ? (int32_t *)take(C * hw * 4) : nullptr;
+        t.hist = out_hist ? (uint64_t *)take(C * 10 * 8) : nullptr;
+        t.ws_bytes = tdk_update_depth_workspace_bytes(C, R, H, W);
+        t.ws = take(t.ws_bytes);
+        if (f) *f = t;
+        return off;
+    };
+    const size_t img_bytes = up256((size_t)U * hw * 8);
+    const size_t slot_bytes = carve(nullptr, 0, nullptr);
+    Arena *ar = nullptr;
+    rc = arena_get(img_bytes + slot_bytes * nslots, &ar);
+    if (rc != TDK_OK) return rc;
+    if ((rc = status_host_get(ar, nchunks)) != TDK_OK) return rc;
+    while ((int64_t)ar->events.size() < nchunks) {
+        cudaEvent_t e;
+        TDK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ar->events.push_back(e);
+    }
+    double *images = (double *)ar->base;
+    FSlot slots[NSTREAM];
+    for (int i = 0; i < nslots; i++) carve((char *)ar->base, img_bytes + slot_bytes * i, &slots[i]);
+    int(*st_host)[TDK_ST_WORDS] = reinterpret_cast<int(*)[TDK_ST_WORDS]>(ar->status_host);
+    std::vector<char> uploaded((size_t)U, 0);
+    std::vector<const double *> kp((size_t)C), rp((size_t)(C * R));
+    cudaStream_t up_stream = ar->streams[0];
+    rc = TDK_OK;
+#define GO(call, what) if (rc == TDK_OK) rc = tdk_check_cuda((call), what)
+    for (int64_t c = 0; c < nchunks && rc == TDK_OK; c++) {
+        const int64_t p0 = c * C, n = (p0 + C <= P) ? C : P - p0;
+        FSlot &f = slots[c % nslots];
+        cudaStream_t st = ar->streams[c % nslots];
+        auto need = [&](int64_t u) {
+            if (!uploaded[u]) {
+                GO(cudaMemcpyAsync(images + (size_t)u * hw, unique[u], hw * 8, cudaMemcpyHostToDevice, up_stream), "H2D image");
+                uploaded[u] = 1;
+            }
+            return (const double *)(images + (size_t)u * hw);
+        };
+        for (int64_t i = 0; i < n; i++) {
+            kp[i] = need(key_slot[p0 + i]);
+            for (int64_t r = 0; r < R; r++) rp[i * R + r] = need(ref_slot[(p0 + i) * R + r]);
+        }
+        GO(cudaEventRecord(ar->events[c], up_stream), "cudaEventRecord");
+        if (st != up_stream) GO(cudaStreamWaitEvent(st, ar->events[c], 0), "cudaStreamWaitEvent");
+        GO(cudaMemcpyAsync(f.cams, key_cams + p0 * 4, n * 4 * 8, cudaMemcpyHostToDevice, st), "H2D key_cams");
+        GO(cudaMemcpyAsync(f.T_wk, T_wk + p0 * 16, n * 16 * 8, cudaMemcpyHostToDevice, st), "H2D T_wk");
+        GO(cudaMemcpyAsync(f.ref_cams, ref_cams + p0 * R * 4, n * R * 4 * 8, cudaMemcpyHostToDevice, st), "H2D ref_cams");
+        GO(cudaMemcpyAsync(f.T_wr, T_wr + p0 * R * 16, n * R * 16 * 8, cudaMemcpyHostToDevice, st), "H2D T_wr");
+        GO(cudaMemcpyAsync(f.age, age + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D age");
+        GO(cudaMemcpyAsync(f.pd, prior_depth + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D prior_depth");
+        GO(cudaMemcpyAsync(f.pv, prior_variance + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D prior_variance");
+        if (f.hist) GO(cudaMemsetAsync(f.hist, 0, n * 10 * 8, st), "memset hist");
+        if (rc == TDK_OK)
+            rc = tdk_update_depth_frames_dev(kp.data(), f.cams, f.T_wk, rp.data(), f.ref_cams, f.T_wr, f.age, f.pd, f.pv,
+                                             params, n, R, H, W, f.od, f.ov, f.of, f.dbg, f.hist, fuse_on_success, f.ws,
+                                             f.ws_bytes, st);
+        GO(cudaMemcpyAsync(out_depth + p0 * hw, f.od, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H depth");
+        GO(cudaMemcpyAsync(out_variance + p0 * hw, f.ov, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H variance");
+        GO(cudaMemcpyAsync(out_flag + p0 * hw, f.of, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H flag");
+        if (dbg_argmin) GO(cudaMemcpyAsync(dbg_argmin + p0 * hw, f.dbg, n * hw * 4, cudaMemcpyDeviceToHost, st), "D2H argmin");
+        if (out_hist) GO(cudaMemcpyAsync(out_hist + p0 * 10, f.hist, n * 10 * 8, cudaMemcpyDeviceToHost, st), "D2H hist");
+        GO(cudaMemcpyAsync(st_host[c], f.ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, st), "D2H status");
+    }
+#undef GO
+    for (int i = 0; i < NSTREAM; i++) {
+        const int rc2 = tdk_check_cuda(cudaStreamSynchronize(ar->streams[i]), "cudaStreamSynchronize");
+        if (rc == TDK_OK) rc = rc2;
+    }
+    if (rc == TDK_OK) rc = status_report(st_host, nchunks);
     return rc;
 }
 

@@ -856,6 +856,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_CTAS) update_depth_tile_kernel(cons
 // its largest magnitude in the workspace; sieve_kernel runs phase A0 on every pixel, stores the
 // final values of every pixel it can decide (and the provisional "failed estimate" values of the
 // others) and appends the undecided pixels of its tile to the keyframe's queue in global memory.
+__device__ __forceinline__ float prep_max(float m, double v)
+{
+    const float av = __double2float_ru(fabs(v));
+    return av == av ? fmaxf(m, av) : INFINITY;   // a NaN in the image switches the cheap path off
+}
+
 __global__ void __launch_bounds__(256) key_prep_kernel(const TdkKeyConst *__restrict__ keys, int p0, size_t hw,
                                                        float *__restrict__ img32, unsigned int *amax)
 {
@@ -863,22 +869,32 @@ __global__ void __launch_bounds__(256) key_prep_kernel(const TdkKeyConst *__rest
     const double *__restrict__ src = keys[pl + p0].img;
     float *__restrict__ dst = img32 + (size_t)pl * hw;
     float m = 0.f;
-    constexpr int PER = 8;   // independent loads in flight per thread
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < hw; i0 += stride * PER) {
-        double v[PER];
+    constexpr int PER = 4;   // independent 16-byte loads in flight per thread
+    const size_t stride = (size_t)gridDim.x * blockDim.x, first = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // pairs of pixels with 16-byte loads and 8-byte stores where the image allows it (the f32 copy
+    // of keyframe pl starts at an even element iff pl * hw is even)
+    const bool wide = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0);
+    const size_t npair = wide ? hw / 2 : 0;
+    const double2 *__restrict__ src2 = reinterpret_cast<const double2 *>(src);
+    float2 *__restrict__ dst2 = reinterpret_cast<float2 *>(dst);
+    for (size_t i0 = first; i0 < npair; i0 += stride * PER) {
+        double2 v[PER];
 #pragma unroll
         for (int k = 0; k < PER; k++) {
             const size_t i = i0 + k * stride;
-            v[k] = i < hw ? __ldg(src + i) : 0.;
+            v[k] = i < npair ? __ldg(src2 + i) : make_double2(0., 0.);
         }
 #pragma unroll
         for (int k = 0; k < PER; k++) {
             const size_t i = i0 + k * stride;
-            if (i < hw) dst[i] = (float)v[k];
-            const float av = __double2float_ru(fabs(v[k]));
-            m = av == av ? fmaxf(m, av) : INFINITY;   // a NaN in the image switches the cheap path off
+            if (i < npair) dst2[i] = make_float2((float)v[k].x, (float)v[k].y);
+            m = prep_max(prep_max(m, v[k].x), v[k].y);
         }
+    }
+    for (size_t i = 2 * npair + first; i < hw; i += stride) {   // the odd last pixel, or the whole image if unaligned
+        const double v = __ldg(src + i);
+        dst[i] = (float)v;
+        m = prep_max(m, v);
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));

@@ -264,6 +264,47 @@ def test_host_pointer_entry_point_matches_device_entry_point():
     assert [int(x) for x in hist.sum(0)] == [int((orc[2] == -k).sum()) for k in range(10)]
 
 
+def test_host_pointer_entry_point_with_shared_frames():
+    """tdk_update_depth_frames_host: frames by pointer, a reference image shared by several
+    keyframes uploaded once; 23 keyframes of 6 scenes so that several chunks and streams are used.
+    Same maps as the oracle on the equivalent [P,R,H,W] batch."""
+    import ctypes as C
+    from tadataka_b200 import _lib
+    base = [scene.make_keyframe(330 + i, R=3, H=240, W=320, cam=scene.CAM_VGA / 2) for i in range(6)]
+    items = []
+    rng = np.random.default_rng(33)
+    for k in range(23):
+        it = dict(base[k % 6])
+        it["prior_variance"] = np.ascontiguousarray(10.0 ** rng.uniform(-3.0, 0.0, size=it["prior_variance"].shape))
+        items.append(it)
+    b = scene.stack_keyframes(items)
+    P, H, W = b["key_img"].shape
+    R = b["ref_imgs"].shape[1]
+    # pointer tables into the six scenes' own images (not into the stacked copy)
+    keep = [np.ascontiguousarray(x["key_img"]) for x in base] + [np.ascontiguousarray(x["ref_imgs"]) for x in base]
+    kp = (C.c_void_p * P)(*[keep[k % 6].ctypes.data for k in range(P)])
+    rp = (C.c_void_p * (P * R))(*[keep[6 + k % 6].ctypes.data + r * H * W * 8 for k in range(P) for r in range(R)])
+    od, ov = np.empty((P, H, W)), np.empty((P, H, W))
+    of = np.empty((P, H, W), dtype=np.int64)
+    am = np.empty((P, H, W), dtype=np.int32)
+    hist = np.zeros((P, 10), dtype=np.uint64)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p)
+
+    rc = _lib.update_depth_frames_host(kp, p(b["key_cam"]), p(b["T_wk"]), rp, p(b["ref_cams"]), p(b["T_wr"]),
+                                       p(b["age"]), p(b["prior_depth"]), p(b["prior_variance"]), p(b["params"]),
+                                       P, R, H, W, p(od), p(ov), p(of), p(am), p(hist), 0)
+    _lib.check(rc)
+    orc = _oracle(b)
+    assert_parity([od, ov, of, am], orc)
+    assert [int(x) for x in hist.sum(0)] == [int((orc[2] == -k).sum()) for k in range(10)]
+    bad = (C.c_void_p * P)(*([None] + [keep[0].ctypes.data] * (P - 1)))
+    assert _lib.update_depth_frames_host(bad, p(b["key_cam"]), p(b["T_wk"]), rp, p(b["ref_cams"]), p(b["T_wr"]),
+                                         p(b["age"]), p(b["prior_depth"]), p(b["prior_variance"]), p(b["params"]),
+                                         P, R, H, W, p(od), p(ov), p(of), None, None, 0) == _lib.ERR_INVALID
+
+
 def _fuse_reference(b, orc):
     """prior (+) oracle measurement where SUCCESS, composed from IEEE numpy ops in the order of
     propagation.rs:27-34 / fusion.rs:3-11."""
