@@ -64,6 +64,7 @@ def parse():
     ap.add_argument("--c4-pairs", type=int, default=64, help="1280x720 pairs per launch (BASELINE.json configs[3])")
     ap.add_argument("--c5-pairs", type=int, default=4096, help="640x480 pairs of the sharded run (configs[4]); 0 = skip")
     ap.add_argument("--c5-chunk", type=int, default=64, help="pairs per round of the sharded run")
+    ap.add_argument("--nccl-default-priority", action="store_true", help="NCCL on a normal-priority stream (experiment)")
     ap.add_argument("--device-scenes", action="store_true",
                     help="render every keyframe's world on the GPU (tdk_render_scene_dev) instead of in numpy")
     ap.add_argument("--plan", type=int, default=-1, help="kernel plan override (2 sorted [default], 0 two kernels, 1 one kernel)")
@@ -368,7 +369,10 @@ def run_b200(args, rank, world, local_rank):
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
         try:
-            dist.init_process_group("nccl", device_id=dev)
+            # NCCL's copy kernels share the SMs with update_depth's grids: on a high-priority stream
+            # their CTAs are placed as soon as a compute CTA retires instead of queueing behind the grid
+            opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=not args.nccl_default_priority)
+            dist.init_process_group("nccl", device_id=dev, pg_options=opts)
             dist.barrier()
             torch.cuda.synchronize()
         finally:
