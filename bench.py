@@ -468,6 +468,36 @@ def run_b200(args, rank, world, local_rank):
                        "what": "depth f64 + variance f64 + flag int8 of every keyframe of every step to rank 0 "
                                "(grouped NCCL send/recv overlapping the next step) + one all-reduce of the "
                                "10-bin histograms", "inside_timed_region": True}
+        # beside it, the same loop with less on the wire: the depth maps only (what BASELINE.json's
+        # configs[4] names) and nothing at all (the kernels alone) -- what the link costs
+        for label, maps in (("depth_maps_only", ("depth",)), ("no_gather", None)):
+            rg2 = sharding.RootGather(world * B, H, W, B, dev, cyclic=True, maps=maps) if maps else None
+            views2 = out if rg2 is None else None
+            for k in range(3 + args.steps):
+                if k == 3:
+                    if rg2 is not None:
+                        rg2.finish()
+                    torch.cuda.synchronize()
+                    barrier()
+                    ev0.record()
+                v = rg2.out_views(k) if rg2 is not None else views2
+                device.update_depth(t["key_img"], t["key_cam"], t["T_wk"], t["ref_imgs"], t["ref_cams"],
+                                    t["T_wr"], t["age"], t["prior_depth"], t["prior_variance"], params,
+                                    check=False, out=v, fuse=True, hist=hist)
+                if rg2 is not None:
+                    rg2.ship(k)
+            if rg2 is not None:
+                rg2.finish()
+            h2 = hist.sum(dim=0)
+            dist.all_reduce(h2)
+            ev1.record()
+            torch.cuda.synchronize()
+            barrier()
+            tm2 = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm2, op=dist.ReduceOp.MAX)
+            gather_info[label] = {"ms_per_step": float(tm2[0]) / args.steps,
+                                  "value": world * B * H * W * args.steps / (float(tm2[0]) * 1e-3)}
+            del rg2
 
     # ---- latency of ONE keyframe (8 references) per launch: "ms per keyframe-pair" without batching
     one = {k: t[k][:1].contiguous() for k in names}

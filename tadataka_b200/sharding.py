@@ -62,10 +62,14 @@ class RootGather:
     gloo on CPU tensors in the tests.  Nothing here runs inside a kernel's inner loop.
     """
 
-    def __init__(self, n_items, H, W, chunk, device, root=0, group=None, cyclic=False):
+    def __init__(self, n_items, H, W, chunk, device, root=0, group=None, cyclic=False,
+                 maps=("depth", "variance", "flag")):
         """cyclic=True: round numbers may run past `rounds` and wrap around (a stream of steps over
-        the same n_items keyframes, each step's results replacing the previous step's on the root)."""
+        the same n_items keyframes, each step's results replacing the previous step's on the root).
+        maps: which of the three result maps travel (the others stay on the rank that made them)."""
         self.group, self.root, self.cyclic = group, root, cyclic
+        self.maps = tuple(maps)
+        self.bytes_per_px = 8 * ("depth" in self.maps) + 8 * ("variance" in self.maps) + 1 * ("flag" in self.maps)
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.n_items, self.H, self.W, self.chunk = n_items, H, W, max(1, int(chunk))
         self.device = torch.device(device)
@@ -141,10 +145,13 @@ class RootGather:
                         continue
                     g = slice(self.spans[r][0] + a, self.spans[r][0] + z)
                     f8 = self._flag8[j % 2][r, :z - a]
-                    ops += [dist.P2POp(dist.irecv, self.depth[g], r, self.group),
-                            dist.P2POp(dist.irecv, self.variance[g], r, self.group),
-                            dist.P2POp(dist.irecv, f8, r, self.group)]
-                    self.bytes_received += (z - a) * self.H * self.W * 17
+                    if "depth" in self.maps:
+                        ops.append(dist.P2POp(dist.irecv, self.depth[g], r, self.group))
+                    if "variance" in self.maps:
+                        ops.append(dist.P2POp(dist.irecv, self.variance[g], r, self.group))
+                    if "flag" in self.maps:
+                        ops.append(dist.P2POp(dist.irecv, f8, r, self.group))
+                    self.bytes_received += (z - a) * self.H * self.W * self.bytes_per_px
                 if ops:
                     works = dist.batch_isend_irecv(ops)
                     self._works[j % 2] = works
@@ -153,11 +160,15 @@ class RootGather:
                 a, z = self.local_span(j)
                 if z > a:
                     d, v, f, f8 = self._buf[j % 2]
-                    f8[:z - a].copy_(f[:z - a])          # int64 -> int8 on the side stream
-                    ops = [dist.P2POp(dist.isend, d[:z - a], self.root, self.group),
-                           dist.P2POp(dist.isend, v[:z - a], self.root, self.group),
-                           dist.P2POp(dist.isend, f8[:z - a], self.root, self.group)]
-                    self._works[j % 2] = dist.batch_isend_irecv(ops)
+                    if "depth" in self.maps:
+                        ops.append(dist.P2POp(dist.isend, d[:z - a], self.root, self.group))
+                    if "variance" in self.maps:
+                        ops.append(dist.P2POp(dist.isend, v[:z - a], self.root, self.group))
+                    if "flag" in self.maps:
+                        f8[:z - a].copy_(f[:z - a])      # int64 -> int8 on the side stream
+                        ops.append(dist.P2POp(dist.isend, f8[:z - a], self.root, self.group))
+                    if ops:
+                        self._works[j % 2] = dist.batch_isend_irecv(ops)
 
     def _widen_done(self, keep=0):
         """Root: widen the int8 flags of every round whose transfer was issued at least `keep`
@@ -170,7 +181,7 @@ class RootGather:
                 if r == self.root:
                     continue
                 a, z = self.local_span(j, r)
-                if z > a:
+                if z > a and "flag" in self.maps:
                     g = slice(self.spans[r][0] + a, self.spans[r][0] + z)
                     self.flag[g].copy_(self._flag8[j % 2][r, :z - a])
             self._works[j % 2] = None

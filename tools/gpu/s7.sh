@@ -1,0 +1,5 @@
+python tools/kbench.py --keyframes 64 --device-scenes --plans 2
+TDK_B200_LIB=tadataka_b200/libtdk_v_stream.so python tools/kbench.py --keyframes 64 --device-scenes --plans 2
+python tools/kbench.py --keyframes 64 --device-scenes --plans 2
+TDK_B200_LIB=tadataka_b200/libtdk_v_stream.so python tools/kbench.py --keyframes 64 --device-scenes --plans 2
+TDK_B200_LIB=tadataka_b200/libtdk_v_stream.so python tools/kbench.py --keyframes 64 --distinct 8 --plans 2

@@ -16,7 +16,16 @@ __global__ void copy16(const uint4 *__restrict__ src, uint4 *__restrict__ dst, s
 __global__ void read16(const uint4 *__restrict__ src, size_t n, unsigned int *sink)
 {
     unsigned int acc = 0;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 7 * stride < n; i += 8 * stride) {   // eight independent 16-byte loads in flight per thread
+        uint4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = src[i + k * stride];
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc ^= v[k].x ^ v[k].y ^ v[k].z ^ v[k].w;
+    }
+    for (; i < n; i += stride) {
         const uint4 v = src[i];
         acc ^= v.x ^ v.y ^ v.z ^ v.w;
     }
@@ -30,7 +39,7 @@ static double run(size_t bytes, int passes, bool read_only)
     cudaMalloc(&a, bytes); cudaMalloc(&b, bytes); cudaMalloc(&sink, 4);
     cudaMemset(a, 1, bytes); cudaMemset(b, 2, bytes);
     const size_t n = bytes / 16;
-    const int blocks = 148 * 8, threads = 512;
+    const int blocks = 148 * 4, threads = 512;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int i = 0; i < 5; i++) {
