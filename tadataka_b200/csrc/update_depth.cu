@@ -347,8 +347,9 @@ __device__ __forceinline__ float sample32(const float *__restrict__ img, int W, 
 {
     const int ix = __float2int_rd(cx), iy = __float2int_rd(cy);
     const float wx = cx - (float)ix, wy = cy - (float)iy;
-    const float *__restrict__ p = img + iy * W + ix;
-    const float a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + W), d = __ldg(p + W + 1);
+    // unsigned 32-bit offsets: one IMAD.WIDE.U32 per address instead of a sign-extended 64-bit chain
+    const unsigned o0 = (unsigned)(iy * W + ix), o1 = o0 + (unsigned)W;
+    const float a = __ldg(img + o0), b = __ldg(img + o0 + 1u), c = __ldg(img + o1), d = __ldg(img + o1 + 1u);
     const float top = __fmaf_rn(wx, b - a, a), bot = __fmaf_rn(wx, d - c, c);
     return __fmaf_rn(wy, bot - top, top);
 }
@@ -387,7 +388,7 @@ __device__ __forceinline__ int phase_a0(const UpdArgs &a, const TdkKeyConst &key
     const int W = a.W;
     const float s0 = sample32(img32, W, x0, y0);
     const float s1 = sample32(img32, W, xf - ax, yf - ay);
-    const float s2 = __ldg(img32 + y * W + x);
+    const float s2 = __ldg(img32 + (unsigned)(y * W + x));
     const float s3 = sample32(img32, W, xf + ax, yf + ay);
     const float s4 = sample32(img32, W, x4, y4);
     const float d0 = s1 - s0, d1 = s2 - s1, d2 = s3 - s2, d3 = s4 - s3;
@@ -924,6 +925,10 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
 
     const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
     const int x = tx * TILE_W + lx, y0 = ty * SIEVE_TILE_H + ly;
+    // per-keyframe base pointers are uniform over the CTA; a pixel is addressed by its unsigned 32-bit
+    // offset inside the keyframe (H * W < 2^31), one IMAD.WIDE.U32 per access
+    const unsigned long long *__restrict__ g_age = reinterpret_cast<const unsigned long long *>(a.age) + map_base;
+    const double *__restrict__ g_pd = a.prior_d + map_base, *__restrict__ g_pv = a.prior_v + map_base;
     // every map load of the thread's pixels goes out first: their DRAM latency overlaps the table
     // set-up below and each other
     uint64_t age[SIEVE_PPT];
@@ -933,8 +938,8 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
         const int y = y0 + k * TILE_H;
         age[k] = 0; d[k] = 0.; v[k] = 0.;
         if (x < W && y < H) {
-            const size_t pix = map_base + (size_t)y * W + x;
-            age[k] = a.age[pix]; d[k] = a.prior_d[pix]; v[k] = a.prior_v[pix];
+            const unsigned o = (unsigned)(y * W + x);
+            age[k] = g_age[o]; d[k] = g_pd[o]; v[k] = g_pv[o];
         }
     }
 
@@ -956,7 +961,7 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
         const bool valid = x < W && y < H;
         int flag = TDK_FLAG_NOT_PROCESSED;
         if (valid) {
-            const size_t pix = map_base + (size_t)y * W + x;
+            const unsigned o = (unsigned)(y * W + x);
             double out_d = d[k];
             if (age[k] != 0) {
                 if (age[k] > (uint64_t)a.R) {
@@ -967,10 +972,10 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
             }
             // undecided pixels get the values a failed estimate keeps; the later kernels overwrite the
             // flag if the exact path fails them and all three values on success
-            a.out_d[pix] = out_d;
-            a.out_v[pix] = v[k];
-            a.out_f[pix] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
-            if (a.dbg) a.dbg[pix] = -1;
+            (a.out_d + map_base)[o] = out_d;
+            (a.out_v + map_base)[o] = v[k];
+            (a.out_f + map_base)[o] = (long long)(flag == 1 ? TDK_FLAG_SUCCESS : flag);
+            if (a.dbg) (a.dbg + map_base)[o] = -1;
             if (a.hist && flag != 1) atomicAdd(&s_hist[-flag], 1u);
         }
         // append this warp's undecided pixels to the keyframe's queue: one global atomic per warp, no CTA barrier
@@ -979,7 +984,7 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
             unsigned int base = 0;
             if (lane == 0) base = atomicAdd(a.cand_count + pl, (unsigned int)__popc(cmask));
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (flag == 1) a.cand[(size_t)pl * hw + base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
+            if (flag == 1) (a.cand + (size_t)pl * hw)[base + __popc(cmask & ((1u << lane) - 1u))] = (unsigned int)(y * W + x);
         }
     }
     if (a.hist) {
