@@ -293,8 +293,8 @@ int tdk_regularize_host(const double *depth, const double *variance, const int64
  *     (the caller computes it, as the reference's loop does): propagate + increment_age, update_depth
  *     against every frame of the ring [fuse_on_success] [regularize], append the frame.  Enqueues
  *     on the mapper's stream and returns without waiting for the GPU; errors of the kind
- *     tdk_update_depth_status reports (age, singular pose, search length) surface in the NEXT
- *     call or in tdk_mapper_sync;
+ *     tdk_update_depth_status reports (age, singular pose, search length) surface at most two
+ *     calls later (a frame's status words are read when their buffer is reused) or in tdk_mapper_sync;
  *   - prune != 0: frames older than the largest age on the map are dropped from the ring (the
  *     reference's TODO, semi_dense_vo.py:202); results do not change, the ring stops growing;
  *     without pruning (or with too small a capacity) a full ring makes track return

@@ -5,8 +5,9 @@
 // plain [R,H,W] blocks without pointer tables, stages the incoming frame through pinned memory
 // (an 8-bit gray / RGB / RGBA frame is converted to the f64 gray image on the device), and never
 // synchronises the host with the GPU inside track(): the status words of a frame's update and the
-// age census that drives the pruning of unused reference frames are read back asynchronously and
-// looked at by the next call.
+// age census that drives the pruning of unused reference frames are read back asynchronously into
+// two alternating host buffers and looked at two calls later, so the host can enqueue frame k + 1
+// while the GPU still works on frame k.
 #include <stdlib.h>
 #include <string.h>
 
@@ -83,12 +84,17 @@ struct tdk_mapper {
     unsigned char *stage[2];
     cudaEvent_t stage_done[2];
     int parity;
-    // results that travel back asynchronously
-    uint64_t *counts_host;
-    int *status_host;
-    cudaEvent_t back_done;
-    int64_t census_n;       // ring length the pending census belongs to (0 = none pending)
-    bool status_pending;
+    // results that travel back asynchronously: frame k uses set k % 2, and track() looks at a set just
+    // before it reuses it -- two frames later, so the host never waits for the frame the GPU is working on
+    struct Back {
+        uint64_t *counts_host;
+        int *status_host;
+        cudaEvent_t done;
+        int64_t census_n;         // ring length the pending census belongs to (0 = none pending)
+        int64_t census_first_id;  // absolute id of the oldest frame the census saw
+        bool status_pending;
+    } back[2];
+    int64_t first_id;       // absolute id (frames since reset) of the frame in ring slot `start`
     int64_t tracked;
 };
 
@@ -142,16 +148,16 @@ int upload_frame(tdk_mapper *m, int64_t slot, const void *image, int format, con
     return TDK_OK;
 }
 
-// Look at what the previous frame sent back: its update's status words and, when pruning is on,
-// the age census that says which reference frames are still in use.
-int collect(tdk_mapper *m)
+// Look at what an earlier frame sent back: its update's status words and, when pruning is on, the
+// age census that says which reference frames are still in use.
+int collect(tdk_mapper *m, tdk_mapper::Back &b, bool apply_census)
 {
-    if (!m->status_pending && m->census_n == 0) return TDK_OK;
-    TDK_CUDA(cudaEventSynchronize(m->back_done));
+    if (!b.status_pending && (b.census_n == 0 || !apply_census)) return TDK_OK;
+    TDK_CUDA(cudaEventSynchronize(b.done));
     int rc = TDK_OK;
-    if (m->status_pending) {
-        m->status_pending = false;
-        const int *s = m->status_host;
+    if (b.status_pending) {
+        b.status_pending = false;
+        const int *s = b.status_host;
         if (s[TDK_ST_SINGULAR]) { tdk_set_error("a reference pose T_wr is singular"); rc = TDK_ERR_SINGULAR; }
         else if (s[TDK_ST_AGE]) { tdk_set_error("Age exceeds the refframe size"); rc = TDK_ERR_AGE; }
         else if (s[TDK_ST_SEARCH_LEN]) {
@@ -159,19 +165,27 @@ int collect(tdk_mapper *m)
             rc = TDK_ERR_SEARCH_LEN;
         }
     }
-    if (m->census_n > 0) {
+    if (apply_census && b.census_n > 0) {
         // update_depth reads refframes[len - age] (semi_dense.rs:207): frames older than the largest
-        // age on the map are dead.  At the next update the ages have grown by one and the ring by
-        // one, so of the n frames the census saw, index n - 1 - oldest is the oldest one still read;
-        // the newest frame always stays (the next propagation needs its pose and camera).
-        const int64_t n = m->census_n;
-        m->census_n = 0;
+        // age on the map are dead, and stay dead -- ages and the ring grow together.  At the update
+        // after the census the ages have grown by one and the ring by one, so of the n frames the
+        // census saw, the one at position n - 1 - oldest is the oldest still read; the newest frame
+        // always stays (the next propagation needs its pose and camera).  Frames are named by their
+        // absolute id, so a census may be applied any number of frames late.
+        const int64_t n = b.census_n;
+        b.census_n = 0;
         int64_t oldest = 0;
         for (int64_t a = 0; a < n + 2; a++)
-            if (m->counts_host[a]) oldest = a;
+            if (b.counts_host[a]) oldest = a;
         int64_t keep_from = n - 1 - oldest;
         if (keep_from > n - 1) keep_from = n - 1;
-        if (keep_from > 0) m->start += keep_from;
+        const int64_t first_live = b.census_first_id + (keep_from > 0 ? keep_from : 0);
+        if (first_live > m->first_id) {
+            int64_t drop = first_live - m->first_id;
+            const int64_t have = m->end - m->start;
+            if (drop > have - 1) drop = have - 1;
+            if (drop > 0) { m->start += drop; m->first_id += drop; }
+        }
     }
     return rc;
 }
@@ -237,10 +251,12 @@ int tdk_mapper_create(void *arena, size_t arena_bytes, int64_t H, int64_t W, int
         rc = tdk_check_cuda(cudaMallocHost((void **)&m->stage[i], stage_bytes), "cudaMallocHost");
         if (rc == TDK_OK) rc = tdk_check_cuda(cudaEventCreateWithFlags(&m->stage_done[i], cudaEventDisableTiming), "cudaEventCreate");
     }
-    if (rc == TDK_OK) rc = tdk_check_cuda(cudaMallocHost((void **)&m->counts_host, (size_t)(capacity + 2) * 8 + 64), "cudaMallocHost");
-    if (rc == TDK_OK) rc = tdk_check_cuda(cudaEventCreateWithFlags(&m->back_done, cudaEventDisableTiming), "cudaEventCreate");
+    for (int i = 0; i < 2 && rc == TDK_OK; i++) {
+        rc = tdk_check_cuda(cudaMallocHost((void **)&m->back[i].counts_host, (size_t)(capacity + 2) * 8 + 64), "cudaMallocHost");
+        if (rc == TDK_OK) rc = tdk_check_cuda(cudaEventCreateWithFlags(&m->back[i].done, cudaEventDisableTiming), "cudaEventCreate");
+        if (rc == TDK_OK) m->back[i].status_host = reinterpret_cast<int *>(m->back[i].counts_host + capacity + 2);
+    }
     if (rc != TDK_OK) { tdk_mapper_destroy(m); return rc; }
-    m->status_host = reinterpret_cast<int *>(m->counts_host + capacity + 2);
     *out = m;
     return TDK_OK;
 }
@@ -253,8 +269,10 @@ void tdk_mapper_destroy(tdk_mapper *m)
         if (m->stage[i]) cudaFreeHost(m->stage[i]);
         if (m->stage_done[i]) cudaEventDestroy(m->stage_done[i]);
     }
-    if (m->counts_host) cudaFreeHost(m->counts_host);
-    if (m->back_done) cudaEventDestroy(m->back_done);
+    for (int i = 0; i < 2; i++) {
+        if (m->back[i].counts_host) cudaFreeHost(m->back[i].counts_host);
+        if (m->back[i].done) cudaEventDestroy(m->back[i].done);
+    }
     delete m;
 }
 
@@ -263,7 +281,8 @@ int tdk_mapper_reset(tdk_mapper *m, const void *image, int image_format, const d
 {
     if (!m || !image || !cam || !T_wf) { tdk_set_error("tdk_mapper_reset: null pointer argument"); return TDK_ERR_INVALID; }
     TDK_CUDA(cudaStreamSynchronize(m->stream));
-    m->start = 0; m->end = 0; m->cur = 0; m->census_n = 0; m->status_pending = false; m->tracked = 0;
+    m->start = 0; m->end = 0; m->cur = 0; m->tracked = 0; m->first_id = 0;
+    for (int i = 0; i < 2; i++) { m->back[i].census_n = 0; m->back[i].status_pending = false; }
     int rc = upload_frame(m, 0, image, image_format, cam, T_wf, nullptr);
     if (rc != TDK_OK) return rc;
     m->end = 1;
@@ -296,7 +315,8 @@ int tdk_mapper_track(tdk_mapper *m, const void *image, int image_format, const d
 {
     if (!m || !image || !cam || !T_wf || !T10) { tdk_set_error("tdk_mapper_track: null pointer argument"); return TDK_ERR_INVALID; }
     if (!m->has_frame) { tdk_set_error("tdk_mapper_track: call tdk_mapper_reset with the first frame"); return TDK_ERR_INVALID; }
-    int rc = collect(m);           // status and census of the previous frame
+    tdk_mapper::Back &b = m->back[m->tracked & 1];
+    int rc = collect(m, b, true);  // status and census of the frame before the previous one
     if (rc != TDK_OK) return rc;
     if (m->end == m->cap && (rc = compact(m)) != TDK_OK) return rc;
     const int64_t slot = m->end, R = m->end - m->start;
@@ -329,17 +349,18 @@ int tdk_mapper_track(tdk_mapper *m, const void *image, int image_format, const d
     m->end = slot + 1;
     m->tracked++;
     // what the next call wants to know: the status words and, when pruning, the age census
-    TDK_CUDA(cudaMemcpyAsync(m->status_host, m->arena + m->l.ws_update, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, m->stream));
-    m->status_pending = true;
+    TDK_CUDA(cudaMemcpyAsync(b.status_host, m->arena + m->l.ws_update, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, m->stream));
+    b.status_pending = true;
     if (m->prune) {
         const int64_t len = m->end - m->start;
         uint64_t *counts = at<uint64_t>(m, m->l.counts);
         rc = tdk_age_usage_dev(at<uint64_t>(m, m->l.age[m->cur]), 1, m->H, m->W, len, counts, m->stream);
         if (rc != TDK_OK) return rc;
-        TDK_CUDA(cudaMemcpyAsync(m->counts_host, counts, (size_t)(len + 2) * 8, cudaMemcpyDeviceToHost, m->stream));
-        m->census_n = len;
+        TDK_CUDA(cudaMemcpyAsync(b.counts_host, counts, (size_t)(len + 2) * 8, cudaMemcpyDeviceToHost, m->stream));
+        b.census_n = len;
+        b.census_first_id = m->first_id;
     }
-    TDK_CUDA(cudaEventRecord(m->back_done, m->stream));
+    TDK_CUDA(cudaEventRecord(b.done, m->stream));
     return TDK_OK;
 }
 
@@ -347,24 +368,30 @@ int tdk_mapper_sync(tdk_mapper *m)
 {
     if (!m) { tdk_set_error("tdk_mapper_sync: null mapper"); return TDK_ERR_INVALID; }
     TDK_CUDA(cudaStreamSynchronize(m->stream));
-    const int64_t census = m->census_n;   // the census stays pending: pruning is applied by the next track()
-    m->census_n = 0;
-    const int rc = collect(m);
-    m->census_n = census;
-    return rc;
+    // status words only: a pending census stays pending, pruning is applied by track()
+    int rc = collect(m, m->back[m->tracked & 1], false);
+    const int rc2 = collect(m, m->back[(m->tracked & 1) ^ 1], false);
+    return rc != TDK_OK ? rc : rc2;
 }
 
 int tdk_mapper_prune(tdk_mapper *m)
 {
     if (!m) { tdk_set_error("tdk_mapper_prune: null mapper"); return TDK_ERR_INVALID; }
+    // whatever is still on its way back is older than the census taken now: apply it first
+    int rc = collect(m, m->back[m->tracked & 1], true);
+    const int rc2 = collect(m, m->back[(m->tracked & 1) ^ 1], true);
+    if (rc == TDK_OK) rc = rc2;
+    if (rc != TDK_OK) return rc;
+    tdk_mapper::Back &b = m->back[0];
     const int64_t len = m->end - m->start;
     uint64_t *counts = at<uint64_t>(m, m->l.counts);
-    int rc = tdk_age_usage_dev(at<uint64_t>(m, m->l.age[m->cur]), 1, m->H, m->W, len, counts, m->stream);
+    rc = tdk_age_usage_dev(at<uint64_t>(m, m->l.age[m->cur]), 1, m->H, m->W, len, counts, m->stream);
     if (rc != TDK_OK) return rc;
-    TDK_CUDA(cudaMemcpyAsync(m->counts_host, counts, (size_t)(len + 2) * 8, cudaMemcpyDeviceToHost, m->stream));
-    m->census_n = len;
-    TDK_CUDA(cudaEventRecord(m->back_done, m->stream));
-    return collect(m);
+    TDK_CUDA(cudaMemcpyAsync(b.counts_host, counts, (size_t)(len + 2) * 8, cudaMemcpyDeviceToHost, m->stream));
+    b.census_n = len;
+    b.census_first_id = m->first_id;
+    TDK_CUDA(cudaEventRecord(b.done, m->stream));
+    return collect(m, b, true);
 }
 
 int tdk_mapper_state(tdk_mapper *m, int64_t *n_frames, size_t *depth_off, size_t *variance_off, size_t *age_off,

@@ -67,6 +67,8 @@ class SemiDenseMapper:
                                       int(self.fuse), int(self.smooth), int(self.prune),
                                       C.c_void_p(torch.cuda.current_stream(self._dev).cuda_stream), C.byref(handle)))
         self._h = handle
+        self._flag_view = None
+        self._cam_cache = (None, None)
         self._last_pose = np.ascontiguousarray(transform_wf, dtype=np.float64)
         dm = None if depth_map is None else np.ascontiguousarray(depth_map, dtype=np.float64)
         vm = None if variance_map is None else np.ascontiguousarray(variance_map, dtype=np.float64)
@@ -78,8 +80,9 @@ class SemiDenseMapper:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
-            _lib.mapper_destroy(h)
+        destroy = getattr(_lib, "mapper_destroy", None)   # may be gone already at interpreter shutdown
+        if h and destroy is not None:
+            destroy(h)
             self._h = None
 
     # ---- state
@@ -116,7 +119,9 @@ class SemiDenseMapper:
 
     @property
     def flag(self):
-        return self._view(self._state()[1][3], torch.int64)
+        if self._flag_view is None:     # the flag map never changes its place in the arena
+            self._flag_view = self._view(self._state()[1][3], torch.int64)
+        return self._flag_view
 
     def reference_images(self):
         """The frames currently held (device tensor [n_frames, H, W], a view of the ring)."""
@@ -131,13 +136,15 @@ class SemiDenseMapper:
         """Advance to a new frame with a known pose (world <- frame).  Returns the flag map (a device
         tensor that the next track() overwrites); the maps are in .depth / .variance / .age.  Does
         not wait for the GPU: an error of this frame's update (an age beyond the ring, a singular
-        pose) is raised by the next track(), maps() or sync()."""
+        pose) is raised by one of the next two track() calls, by maps() or by sync()."""
         image, fmt = _image_format(image)
         if image.shape[:2] != self.shape:
             raise ValueError("every frame must have the first frame's shape")
         T_w1 = np.ascontiguousarray(transform_wf, dtype=np.float64)
         T10 = np.ascontiguousarray(np.linalg.inv(T_w1) @ self._last_pose)   # semi_dense_vo.py: transform10
-        _lib.check(_lib.mapper_track(self._h, _p(image), fmt, _p(camera_vector(camera_params)), _p(T_w1), _p(T10)))
+        if self._cam_cache[0] is not camera_params:      # the same camera object frame after frame
+            self._cam_cache = (camera_params, camera_vector(camera_params))
+        _lib.check(_lib.mapper_track(self._h, _p(image), fmt, _p(self._cam_cache[1]), _p(T_w1), _p(T10)))
         self._last_pose = T_w1
         return self.flag
 
