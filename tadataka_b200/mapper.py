@@ -68,7 +68,6 @@ class SemiDenseMapper:
                                       C.c_void_p(torch.cuda.current_stream(self._dev).cuda_stream), C.byref(handle)))
         self._h = handle
         self._flag_view = None
-        self._cam_cache = (None, None)
         self._last_pose = np.ascontiguousarray(transform_wf, dtype=np.float64)
         dm = None if depth_map is None else np.ascontiguousarray(depth_map, dtype=np.float64)
         vm = None if variance_map is None else np.ascontiguousarray(variance_map, dtype=np.float64)
@@ -142,9 +141,7 @@ class SemiDenseMapper:
             raise ValueError("every frame must have the first frame's shape")
         T_w1 = np.ascontiguousarray(transform_wf, dtype=np.float64)
         T10 = np.ascontiguousarray(np.linalg.inv(T_w1) @ self._last_pose)   # semi_dense_vo.py: transform10
-        if self._cam_cache[0] is not camera_params:      # the same camera object frame after frame
-            self._cam_cache = (camera_params, camera_vector(camera_params))
-        _lib.check(_lib.mapper_track(self._h, _p(image), fmt, _p(self._cam_cache[1]), _p(T_w1), _p(T10)))
+        _lib.check(_lib.mapper_track(self._h, _p(image), fmt, _p(camera_vector(camera_params)), _p(T_w1), _p(T10)))
         self._last_pose = T_w1
         return self.flag
 
