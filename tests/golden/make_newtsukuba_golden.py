@@ -8,6 +8,11 @@ poses and intrinsics `NewTsukubaDataset` would produce (tadataka/dataset/new_tsu
 153-158), so that the replayable cases of tests/vo/semi_dense/test_semi_dense.py:104-134 and the
 `test_update_depth` smoke (:40-73) can be re-run on the GPU box, where /root/reference is absent.
 The oracle's outputs on that pair are stored next to the inputs as the golden answers.
+
+Note: the maps stored here come from the repo's own oracle, not from a build of the reference (no
+Rust toolchain): they pin GPU-vs-oracle.  The reference-held evidence is the primitives' vectors
+(tests/test_oracle_golden.py), the five flag cases and the flag histogram; tests/test_oracle_chain.py
+ties the oracle's success path to those primitives.
 """
 import os
 import sys
