@@ -568,6 +568,14 @@ def run_b200(args, rank, world, local_rank):
         c3_ms, c3_f64_ms = c3["u8"], c3["f64"]
         del mapper
 
+    # ---- the companion kernels on 64 VGA frames (increment_age, propagate, fusion, regularize)
+    companions = None
+    if rank == 0 and world == 1 and not args.no_c4:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import companion_bench
+        companions = companion_bench.run(frames=64, iters=10)
+        torch.cuda.empty_cache()
+
     # ---- C5: the sharded run with the gather inside the clock (all ranks take part)
     c5 = None
     if args.c5_pairs > 0:
@@ -674,7 +682,7 @@ def run_b200(args, rank, world, local_rank):
             "c4_720p_ms_per_pair": c4_ms, "c4_pairs_per_launch": args.c4_pairs if c4_ms is not None else None,
             "c3_vo_loop_ms_per_frame": c3_ms, "c3_vo_loop_f64_frames_ms_per_frame": c3_f64_ms,
             "c3_frames": "30 x 640x480, 8-bit gray frames from the host, one tdk_mapper_track call per frame",
-            "c5": c5,
+            "companions": companions, "c5": c5,
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
