@@ -298,12 +298,6 @@ __global__ void __launch_bounds__(TPB, TDK_FOLD_MIN_CTAS) prop_fold_kernel(const
     // the first four sources of the list, 0xffffffff where it is shorter
     unsigned int a = h - 1u, b = 0xffffffffu, c = 0xffffffffu, d = 0xffffffffu, more = 0u;
     unsigned int link = nx[a];
-    if (link == 0u) {   // one source, nothing to fold: the case of nearly every target under an ordinary motion
-        depth1[g] = sd[a];
-        variance1[g] = sv[a];
-        if (age1) age1[g] = age0[(size_t)p * hw + a] + 1ull;
-        return;
-    }
     if (link) { b = link - 1u; link = nx[b]; }
     if (link) { c = link - 1u; link = nx[c]; }
     if (link) { d = link - 1u; more = nx[d]; }
