@@ -149,6 +149,7 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
                           double *out_depth, double *out_variance, int64_t *out_flag,
                           int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success)
 {
+    TdkRange range("tdk_update_depth_host");
     if (!key_imgs || !ref_imgs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
         !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
         tdk_set_error("tdk_update_depth_host: null pointer argument");
@@ -251,6 +252,7 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
                                  double *out_variance, int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
                                  int fuse_on_success)
 {
+    TdkRange range("tdk_update_depth_frames_host");
     if (!key_img_ptrs || !ref_img_ptrs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
         !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
         tdk_set_error("tdk_update_depth_frames_host: null pointer argument");
@@ -474,6 +476,7 @@ int down(Stage &s, void *dst, const void *src, size_t bytes)
 int tdk_increment_age_host(const uint64_t *age0, const double *cam0, const double *cam1, const double *T10,
                            const double *depth0, int64_t P, int64_t H, int64_t W, uint64_t *age1)
 {
+    TdkRange range("tdk_increment_age_host");
     if (!age0 || !cam0 || !cam1 || !T10 || !depth0 || !age1 || P <= 0 || H <= 0 || W <= 0) {
         tdk_set_error("tdk_increment_age_host: bad argument");
         return TDK_ERR_INVALID;
@@ -502,6 +505,7 @@ int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1
                        const double *variance0, int64_t P, int64_t H, int64_t W, double default_depth,
                        double default_variance, double uncertaintity_bias, double *depth1, double *variance1)
 {
+    TdkRange range("tdk_propagate_host");
     if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || P <= 0 || H <= 0 || W <= 0) {
         tdk_set_error("tdk_propagate_host: bad argument");
         return TDK_ERR_INVALID;
@@ -531,6 +535,7 @@ int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1
 int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, const double *var2,
                     const int64_t *flag, int64_t n, int depth_domain, double *mu, double *var)
 {
+    TdkRange range("tdk_fusion_host");
     if (!mu1 || !mu2 || !var1 || !var2 || !mu || !var || n <= 0) {
         tdk_set_error("tdk_fusion_host: bad argument");
         return TDK_ERR_INVALID;
@@ -558,6 +563,7 @@ int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, co
 int tdk_regularize_host(const double *depth, const double *variance, const int64_t *flag, int64_t P, int64_t H,
                         int64_t W, double *out_depth)
 {
+    TdkRange range("tdk_regularize_host");
     if (!depth || !variance || !flag || !out_depth || P <= 0 || H <= 0 || W <= 0) {
         tdk_set_error("tdk_regularize_host: bad argument");
         return TDK_ERR_INVALID;

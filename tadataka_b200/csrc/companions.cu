@@ -515,6 +515,7 @@ static int propagate_launch(const char *who, const double *T10, const double *ca
                             double uncertaintity_bias, double *depth1, double *variance1, uint64_t *age1,
                             void *workspace, size_t workspace_bytes, void *stream)
 {
+    TdkRange range("tdk_propagate");
     if (!T10 || !cam0 || !cam1 || !depth0 || !variance0 || !depth1 || !variance1 || !workspace ||
         ((age0 == nullptr) != (age1 == nullptr))) {
         tdk_set_error("%s: null pointer argument", who);

@@ -313,6 +313,7 @@ int tdk_mapper_reset(tdk_mapper *m, const void *image, int image_format, const d
 int tdk_mapper_track(tdk_mapper *m, const void *image, int image_format, const double *cam, const double *T_wf,
                      const double *T10)
 {
+    TdkRange range("tdk_mapper_track");
     if (!m || !image || !cam || !T_wf || !T10) { tdk_set_error("tdk_mapper_track: null pointer argument"); return TDK_ERR_INVALID; }
     if (!m->has_frame) { tdk_set_error("tdk_mapper_track: call tdk_mapper_reset with the first frame"); return TDK_ERR_INVALID; }
     tdk_mapper::Back &b = m->back[m->tracked & 1];

@@ -1386,6 +1386,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
            uint64_t *out_hist, int fuse, int plan, void *workspace, size_t workspace_bytes,
            cudaStream_t stream)
 {
+    TdkRange range("tdk_update_depth");
     if (!key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth || !prior_variance ||
         !params || !out_depth || !out_variance || !out_flag || !workspace ||
         (!key_imgs && !key_ptrs_host) || (!ref_imgs && !ref_ptrs_host)) {
