@@ -343,6 +343,19 @@ int tdk_transform_dev(const double *T10, const double *ps0, int64_t n, double *p
 int tdk_calc_depth0_dev(const double *T10, const double *xs0, const double *xs1, int64_t n,
                         double *depths0, void *stream);
 
+/* Host-pointer forms of the same helpers: numpy in, numpy out, one call, as the pyo3 functions
+ * cited above have them.  tdk_interpolate_host returns TDK_ERR_RANGE when a coordinate lies outside
+ * the image (tadataka/interpolation/__init__.py:23-29 raises ValueError there). */
+int tdk_warp_vecs_host(const double *T10, const double *xs0, const double *depths0, int64_t n,
+                       double *xs1, double *depths1);
+int tdk_interpolate_host(const double *image, int64_t H, int64_t W, const double *coords, int64_t n,
+                         double *out);
+int tdk_project_vecs_host(const double *ps, int64_t n, double *xs);
+int tdk_inv_project_vecs_host(const double *xs, const double *depths, int64_t n, double *ps);
+int tdk_transform_host(const double *T10, const double *ps0, int64_t n, double *ps1);
+int tdk_calc_depth0_host(const double *T10, const double *xs0, const double *xs1, int64_t n,
+                         double *depths0);
+
 /* Synthetic-scene ray-caster (SURVEY 8d workload, 8f rank 3); no counterpart in the reference,
  * which reads its frames from datasets.  Renders N views of one piecewise-planar world, one thread
  * per pixel, without any graphics API: the device version of tadataka_b200/scene.py World.render.

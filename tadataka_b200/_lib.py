@@ -85,6 +85,12 @@ project_vecs_dev = _sig("tdk_project_vecs_dev", C.c_int, P, I64, P, P)
 inv_project_vecs_dev = _sig("tdk_inv_project_vecs_dev", C.c_int, P, P, I64, P, P)
 transform_dev = _sig("tdk_transform_dev", C.c_int, P, P, I64, P, P)
 calc_depth0_dev = _sig("tdk_calc_depth0_dev", C.c_int, P, P, P, I64, P, P)
+warp_vecs_host = _sig("tdk_warp_vecs_host", C.c_int, P, P, P, I64, P, P)
+interpolate_host = _sig("tdk_interpolate_host", C.c_int, P, I64, I64, P, I64, P)
+project_vecs_host = _sig("tdk_project_vecs_host", C.c_int, P, I64, P)
+inv_project_vecs_host = _sig("tdk_inv_project_vecs_host", C.c_int, P, P, I64, P)
+transform_host = _sig("tdk_transform_host", C.c_int, P, P, I64, P)
+calc_depth0_host = _sig("tdk_calc_depth0_host", C.c_int, P, P, P, I64, P)
 age_usage_dev = _sig("tdk_age_usage_dev", C.c_int, P, I64, I64, I64, I64, P, P)
 render_scene_dev = _sig("tdk_render_scene_dev", C.c_int, P, P, P, I64, C.c_double, P, P, I64, I64, I64, P, P, P)
 sqrt_threshold = _sig("tdk_sqrt_threshold", C.c_double, C.c_double)
@@ -116,7 +122,8 @@ EXPORTS = [
     "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
     "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
     "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",
-    "tdk_update_depth_frames_host", "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev", "tdk_set_subpixel_refinement",
+    "tdk_update_depth_frames_host", "tdk_warp_vecs_host", "tdk_interpolate_host", "tdk_project_vecs_host",
+    "tdk_inv_project_vecs_host", "tdk_transform_host", "tdk_calc_depth0_host", "tdk_dvo_tukey_workspace_bytes", "tdk_dvo_tukey_scale_dev", "tdk_set_subpixel_refinement",
 ]
 
 

@@ -585,3 +585,113 @@ int tdk_regularize_host(const double *depth, const double *variance, const int64
 }
 
 }  // extern "C"
+
+// ---- host-pointer forms of the helpers on the drop-in surface (src/py/{warp,interpolation,projection,
+// transform,triangulation}.rs: numpy in, numpy out)
+namespace {
+struct In { const void *host; size_t bytes; };
+struct Out { void *host; size_t bytes; };
+// copy the inputs up, run `body(device inputs, device outputs, stream)`, copy the outputs back
+template <int NI, int NO, typename Body>
+int run_staged(const char *who, const In (&in)[NI], const Out (&out)[NO], Body body)
+{
+    TdkRange range(who);
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    size_t total = 0;
+    for (int i = 0; i < NI; i++) total += up256(in[i].bytes);
+    for (int i = 0; i < NO; i++) total += up256(out[i].bytes);
+    Stage s;
+    TDK_RC(stage_open(total + 256, &s));
+    void *din[NI], *dout[NO];
+    for (int i = 0; i < NI; i++) {
+        din[i] = s.take(in[i].bytes);
+        if (in[i].bytes) TDK_RC(up(s, din[i], in[i].host, in[i].bytes));
+    }
+    for (int i = 0; i < NO; i++) dout[i] = s.take(out[i].bytes);
+    TDK_RC(body(din, dout, s.st));
+    for (int i = 0; i < NO; i++)
+        if (out[i].bytes) TDK_RC(down(s, out[i].host, dout[i], out[i].bytes));
+    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+}
+}  // namespace
+
+extern "C" {
+
+int tdk_warp_vecs_host(const double *T10, const double *xs0, const double *depths0, int64_t n, double *xs1, double *depths1)
+{
+    if (!T10 || !xs0 || !depths0 || !xs1 || !depths1 || n < 0) { tdk_set_error("tdk_warp_vecs_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    const In in[3] = {{T10, 128}, {xs0, (size_t)n * 16}, {depths0, (size_t)n * 8}};
+    const Out out[2] = {{xs1, (size_t)n * 16}, {depths1, (size_t)n * 8}};
+    return run_staged("tdk_warp_vecs_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        return tdk_warp_vecs_dev((const double *)i[0], (const double *)i[1], (const double *)i[2], n, (double *)o[0], (double *)o[1], st);
+    });
+}
+
+int tdk_interpolate_host(const double *image, int64_t H, int64_t W, const double *coords, int64_t n, double *out_values)
+{
+    if (!image || !coords || !out_values || H <= 0 || W <= 0 || n < 0) { tdk_set_error("tdk_interpolate_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    int32_t status = 0;
+    const In in[2] = {{image, (size_t)H * W * 8}, {coords, (size_t)n * 16}};
+    const Out out[2] = {{out_values, (size_t)n * 8}, {&status, 4}};
+    int rc = run_staged("tdk_interpolate_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        int r = tdk_check_cuda(cudaMemsetAsync(o[1], 0, 4, st), "cudaMemsetAsync");
+        if (r != TDK_OK) return r;
+        return tdk_interpolate_dev((const double *)i[0], H, W, (const double *)i[1], n, (double *)o[0], (int32_t *)o[1], st);
+    });
+    if (rc == TDK_OK && status != 0) {
+        // tadataka/interpolation/__init__.py:23-29 raises ValueError for such coordinates
+        tdk_set_error("Coordinates out of image range");
+        return TDK_ERR_RANGE;
+    }
+    return rc;
+}
+
+int tdk_project_vecs_host(const double *ps, int64_t n, double *xs)
+{
+    if (!ps || !xs || n < 0) { tdk_set_error("tdk_project_vecs_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    const In in[1] = {{ps, (size_t)n * 24}};
+    const Out out[1] = {{xs, (size_t)n * 16}};
+    return run_staged("tdk_project_vecs_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        return tdk_project_vecs_dev((const double *)i[0], n, (double *)o[0], st);
+    });
+}
+
+int tdk_inv_project_vecs_host(const double *xs, const double *depths, int64_t n, double *ps)
+{
+    if (!xs || !depths || !ps || n < 0) { tdk_set_error("tdk_inv_project_vecs_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    const In in[2] = {{xs, (size_t)n * 16}, {depths, (size_t)n * 8}};
+    const Out out[1] = {{ps, (size_t)n * 24}};
+    return run_staged("tdk_inv_project_vecs_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        return tdk_inv_project_vecs_dev((const double *)i[0], (const double *)i[1], n, (double *)o[0], st);
+    });
+}
+
+int tdk_transform_host(const double *T10, const double *ps0, int64_t n, double *ps1)
+{
+    if (!T10 || !ps0 || !ps1 || n < 0) { tdk_set_error("tdk_transform_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    const In in[2] = {{T10, 128}, {ps0, (size_t)n * 24}};
+    const Out out[1] = {{ps1, (size_t)n * 24}};
+    return run_staged("tdk_transform_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        return tdk_transform_dev((const double *)i[0], (const double *)i[1], n, (double *)o[0], st);
+    });
+}
+
+int tdk_calc_depth0_host(const double *T10, const double *xs0, const double *xs1, int64_t n, double *depths0)
+{
+    if (!T10 || !xs0 || !xs1 || !depths0 || n < 0) { tdk_set_error("tdk_calc_depth0_host: bad argument"); return TDK_ERR_INVALID; }
+    if (n == 0) return TDK_OK;
+    const In in[3] = {{T10, 128}, {xs0, (size_t)n * 16}, {xs1, (size_t)n * 16}};
+    const Out out[1] = {{depths0, (size_t)n * 8}};
+    return run_staged("tdk_calc_depth0_host", in, out, [&](void **i, void **o, cudaStream_t st) {
+        return tdk_calc_depth0_dev((const double *)i[0], (const double *)i[1], (const double *)i[2], n, (double *)o[0], st);
+    });
+}
+
+}  // extern "C"
