@@ -321,13 +321,19 @@ def run_c5(args, rank, world, dev, barrier):
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         res[label] = float(tm[0])
     flags = [int(x) for x in total.tolist()]
+    # size-independent checks at the full size: every pixel of every pair carries exactly one flag, and
+    # the flag maps that ARRIVED on rank 0 count as many successes as the all-reduced histogram says
+    checks = {"histogram_covers_every_pixel": sum(flags) == n * H * W}
+    if rank == 0:
+        gathered_flag = rg.flag if rg is not None else out[2]
+        checks["gathered_flag_maps_match_histogram"] = int((gathered_flag == 0).sum()) == flags[0]
     block = {
         "workload": f"C5: {n} x (640x480 keyframe vs 1 reference frame), sharded over {world} GPU(s) "
                     f"in rounds of {chunk}, every pair its own CUDA-rendered world",
         "pairs": n, "scaling": "strong", "total_ms": res["total"], "ms_per_pair": res["total"] / n,
         "pixels_per_s": n * H * W / (res["total"] * 1e-3),
         "compute_only_ms": res["compute_only"],
-        "flag_histogram": flags, "success_px": flags[0],
+        "flag_histogram": flags, "success_px": flags[0], "checks": checks,
     }
     if world > 1:
         rx = rg.bytes_received / 2 if rank == 0 else 0      # two passes shipped (warm-up + timed)
