@@ -354,12 +354,39 @@ __device__ __forceinline__ float sample32(const float *__restrict__ img, int W, 
     return __fmaf_rn(wy, bot - top, top);
 }
 
+// Key tile staged in shared memory by the TMA engine (sieve variant, see update_depth_sieve_kernel):
+// the f32 key pixels of the CTA's 64 x (4 PPT) tile plus ST_HALO pixels on every side.
+constexpr int ST_HALO = 16;
+constexpr int ST_W = TILE_W + 2 * ST_HALO;
+struct KeyTile {
+    const float *s;    // shared memory, row pitch ST_W; nullptr = no tile, sample global memory
+    int x0, y0, rows;  // image coordinates of the tile's first element, number of rows
+};
+
+// f32 bilinear sample out of the staged tile; (ix, iy) = floor of the coordinates, already known to lie
+// inside the tile with their +1 neighbours
+__device__ __forceinline__ float sample32_tile(const KeyTile &t, float cx, float cy)
+{
+    const int ix = __float2int_rd(cx), iy = __float2int_rd(cy);
+    const float wx = cx - (float)ix, wy = cy - (float)iy;
+    const float *p = t.s + (iy - t.y0) * ST_W + (ix - t.x0);
+    const float a = p[0], b = p[1], c = p[ST_W], d = p[ST_W + 1];
+    const float top = __fmaf_rn(wx, b - a, a), bot = __fmaf_rn(wx, d - c, c);
+    return __fmaf_rn(wy, bot - top, top);
+}
+
+__device__ __forceinline__ bool tile_holds(const KeyTile &t, float cx, float cy)
+{
+    const int ix = __float2int_rd(cx) - t.x0, iy = __float2int_rd(cy) - t.y0;
+    return ix >= 0 && ix < ST_W - 1 && iy >= 0 && iy < t.rows - 1;
+}
+
 // Phase A0 for pixel (x, y) with prior (d, v) and 0 < age <= R.  Returns a final flag (<= 0) or
 // 1 = undecided (the exact path has to look at it).  out_d as in phase_a1.  thr2: the keyframe's
 // threshold on the f32 sum of squared differences (negative: certify nothing).
 __device__ __forceinline__ int phase_a0(const UpdArgs &a, const TdkKeyConst &key, const float *__restrict__ img32,
                                         int p, int x, int y, double xk, double yk, uint64_t age, double d,
-                                        double v, float thr2, double &out_d)
+                                        double v, float thr2, double &out_d, const KeyTile tile = KeyTile{nullptr, 0, 0, 0})
 {
     out_d = d;
     const double idp = tdk::inv(d);
@@ -386,11 +413,21 @@ __device__ __forceinline__ int phase_a0(const UpdArgs &a, const TdkKeyConst &key
         return out ? TDK_FLAG_KEY_OUT_OF_RANGE : 1;
     }
     const int W = a.W;
-    const float s0 = sample32(img32, W, x0, y0);
-    const float s1 = sample32(img32, W, xf - ax, yf - ay);
-    const float s2 = __ldg(img32 + (unsigned)(y * W + x));
-    const float s3 = sample32(img32, W, xf + ax, yf + ay);
-    const float s4 = sample32(img32, W, x4, y4);
+    float s0, s1, s2, s3, s4;
+    if (tile.s && tile_holds(tile, x0, y0) && tile_holds(tile, x4, y4)) {
+        // the segment is straight: with both ends inside the tile every sample is
+        s0 = sample32_tile(tile, x0, y0);
+        s1 = sample32_tile(tile, xf - ax, yf - ay);
+        s2 = tile.s[(y - tile.y0) * ST_W + (x - tile.x0)];
+        s3 = sample32_tile(tile, xf + ax, yf + ay);
+        s4 = sample32_tile(tile, x4, y4);
+    } else {
+        s0 = sample32(img32, W, x0, y0);
+        s1 = sample32(img32, W, xf - ax, yf - ay);
+        s2 = __ldg(img32 + (unsigned)(y * W + x));
+        s3 = sample32(img32, W, xf + ax, yf + ay);
+        s4 = sample32(img32, W, x4, y4);
+    }
     const float d0 = s1 - s0, d1 = s2 - s1, d2 = s3 - s2, d3 = s4 - s3;
     const float S = __fmaf_rn(d3, d3, __fmaf_rn(d2, d2, __fmaf_rn(d1, d1, d0 * d0)));
     return S < thr2 ? TDK_FLAG_INSUFFICIENT_GRADIENT : 1;
@@ -915,12 +952,38 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     __shared__ double s_xk[TILE_W], s_yk[SIEVE_TILE_H];
     __shared__ unsigned int s_hist[10];
     __shared__ float s_thr2;
+#ifdef TDK_SIEVE_TMA
+    // the CTA's key tile + halo, fetched row by row by the TMA engine (cp.async.bulk, one elected
+    // thread, completion counted in bytes on an mbarrier) while the threads load their maps and run
+    // the exact part of phase A0
+    constexpr int ST_H = SIEVE_TILE_H + 2 * ST_HALO;
+    __shared__ __align__(128) float s_tile[ST_H * ST_W];
+    __shared__ __align__(8) unsigned long long s_bar;
+#endif
 
     const int tid = threadIdx.x;
     const int pl = blockIdx.z, p = pl + a.p0;
     const int ty = blockIdx.y, tx = blockIdx.x;
     const int W = a.W, H = a.H;
     const size_t hw = (size_t)H * W, map_base = (size_t)p * hw;
+#ifdef TDK_SIEVE_TMA
+    const int rx0 = tx * TILE_W - ST_HALO, ry0 = ty * SIEVE_TILE_H - ST_HALO;
+    const bool use_tile = (W & 3) == 0;   // 16-byte granularity of the bulk copies
+    if (use_tile && tid == 0) {
+        const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const int cx0 = rx0 < 0 ? 0 : rx0, cx1 = min(W, rx0 + ST_W);
+        const int gy0 = ry0 < 0 ? 0 : ry0, gy1 = min(H, ry0 + ST_H);
+        const unsigned row_bytes = (unsigned)(cx1 - cx0) * 4u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(row_bytes * (unsigned)(gy1 - gy0)) : "memory");
+        const float *src = a.img32 + (size_t)pl * hw + (size_t)gy0 * W + cx0;
+        unsigned dst = (unsigned)__cvta_generic_to_shared(s_tile + (gy0 - ry0) * ST_W + (cx0 - rx0));
+        for (int gy = gy0; gy < gy1; gy++, src += W, dst += ST_W * 4)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                         "r"(row_bytes), "r"(bar) : "memory");
+    }
+#endif
     const TdkKeyConst key = a.keys[p];
 
     const int lx = tid & (TILE_W - 1), ly = tid / TILE_W;
@@ -955,6 +1018,16 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
     const float thr2 = s_thr2;
     const double xk = s_xk[lx];
     const int lane = tid & 31;
+#ifdef TDK_SIEVE_TMA
+    KeyTile tile{nullptr, rx0, ry0, ST_H};
+    if (use_tile) {   // the barrier was initialised before the __syncthreads above; phase 0 completes when every row has landed
+        const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+        asm volatile("{\n .reg .pred p;\n TDK_WAIT:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n @p bra TDK_DONE;\n bra TDK_WAIT;\n TDK_DONE:\n}" ::"r"(bar) : "memory");
+        tile.s = s_tile;
+    }
+#else
+    const KeyTile tile{nullptr, 0, 0, 0};
+#endif
 #pragma unroll
     for (int k = 0; k < SIEVE_PPT; k++) {
         const int y = y0 + k * TILE_H;
@@ -967,7 +1040,7 @@ __global__ void __launch_bounds__(BLOCK, SIEVE_MIN_CTAS) update_depth_sieve_kern
                 if (age[k] > (uint64_t)a.R) {
                     atomicExch(&a.status[TDK_ST_AGE], 1);
                 } else {
-                    flag = phase_a0(a, key, img32, p, x, y, xk, s_yk[ly + k * TILE_H], age[k], d[k], v[k], thr2, out_d);
+                    flag = phase_a0(a, key, img32, p, x, y, xk, s_yk[ly + k * TILE_H], age[k], d[k], v[k], thr2, out_d, tile);
                 }
             }
             // undecided pixels get the values a failed estimate keeps; the later kernels overwrite the
