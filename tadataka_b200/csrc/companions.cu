@@ -50,7 +50,10 @@ constexpr int RT_W = 64, RT_H = 4;      // source tiles of the forward-warp kern
 #define TDK_SCATTER_MIN_CTAS 8   // these kernels wait on loads and atomics: 64 resident warps beat 32 (9.5 vs 11.3 us per frame)
 #endif
 constexpr int SCATTER_MIN_CTAS = TDK_SCATTER_MIN_CTAS;
-constexpr int REG_W = 64, REG_H = 16;   // regularize tile
+#ifndef TDK_REG_H
+#define TDK_REG_H 8    // 2.47 us per VGA frame against 2.57 at 16 rows and 2.80 at 32: more, smaller CTAs hide the staging latency better
+#endif
+constexpr int REG_W = 64, REG_H = TDK_REG_H;   // regularize tile
 __global__ void __launch_bounds__(TPB) regularize_kernel(const double *__restrict__ depth,
                                                          const double *__restrict__ variance,
                                                          const long long *__restrict__ flag, int P, int H,
