@@ -45,7 +45,11 @@ __global__ void __launch_bounds__(TPB) fusion_kernel(const double *__restrict__ 
 // A CTA stages id*iv and iv of its 64x16 tile plus a one-pixel halo in shared memory (two
 // inversions per pixel instead of two per neighbour visit; 18 rows read for 16 written); cells the
 // reference skips hold exact zeros, which leave its left-to-right sums unchanged.
-constexpr int RT_W = 64, RT_H = 4;      // source tiles of the forward-warp kernels below
+#ifndef TDK_SCATTER_PPT
+#define TDK_SCATTER_PPT 4   // increment_age 4.37 / 3.70 / 3.45 us per VGA frame at 1 / 2 / 4 pixels per thread, propagate 8.18 / 7.88 / 7.79
+#endif
+constexpr int RT_W = 64, RT_ROWS = 4, SC_PPT = TDK_SCATTER_PPT;   // source tiles of the forward-warp kernels below:
+constexpr int RT_H = RT_ROWS * SC_PPT;                            // 64 x (4 PPT) pixels, PPT pixels per thread (rows ly, ly + 4, ...)
 #ifndef TDK_SCATTER_MIN_CTAS
 #define TDK_SCATTER_MIN_CTAS 8   // these kernels wait on loads and atomics: 64 resident warps beat 32 (9.5 vs 11.3 us per frame)
 #endif
@@ -158,19 +162,12 @@ __device__ __forceinline__ int warp_target_n(const FrameConst &c, double qx, dou
 // with the largest linear index (atomicMax), then one gather pass writes age0[winner] + 1.
 // Source pixels are visited in 64x4 tiles; K0^-1 u0 depends on the column (row) only, so a tile
 // computes 64 + 4 divisions instead of two per pixel (camera.rs:55-57).
-__device__ __forceinline__ bool tile_source(const FrameConst &c, int H, int W, double *s_qx, double *s_qy,
-                                            int &x, int &y, double &qx, double &qy)
+__device__ __forceinline__ void tile_tables(const FrameConst &c, double *s_qx, double *s_qy)
 {
     const int tid = threadIdx.x;
     if (tid < RT_W) s_qx[tid] = ((double)(blockIdx.x * RT_W + tid) - c.o0x) / c.f0x;
     else if (tid < RT_W + RT_H) s_qy[tid - RT_W] = ((double)(blockIdx.y * RT_H + tid - RT_W) - c.o0y) / c.f0y;
     __syncthreads();
-    const int lx = tid & (RT_W - 1), ly = tid / RT_W;
-    x = blockIdx.x * RT_W + lx;
-    y = blockIdx.y * RT_H + ly;
-    qx = s_qx[lx];
-    qy = s_qy[ly];
-    return x < W && y < H;
 }
 
 __global__ void __launch_bounds__(TPB, SCATTER_MIN_CTAS) age_scatter_kernel(const double *__restrict__ T10,
@@ -183,12 +180,25 @@ __global__ void __launch_bounds__(TPB, SCATTER_MIN_CTAS) age_scatter_kernel(cons
     const int p = blockIdx.z;
     const int hw = H * W;
     const FrameConst c = load_frame_const(T10, cam0, cam1, p);
-    int x, y;
-    double qx, qy, d1;
-    if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
-    const int s = y * W + x;
-    const int t = warp_target_n(c, qx, qy, depth0[(size_t)p * hw + s], H, W, d1);
-    if (t >= 0) atomicMax(winner + (size_t)p * hw + t, (unsigned int)s + 1u);
+    const int lx = threadIdx.x & (RT_W - 1), ly = threadIdx.x / RT_W;
+    const int x = blockIdx.x * RT_W + lx;
+    double d0[SC_PPT];
+#pragma unroll
+    for (int k = 0; k < SC_PPT; k++) {   // every depth load of the thread is in flight before the tables are built
+        const int y = blockIdx.y * RT_H + ly + k * RT_ROWS;
+        d0[k] = (x < W && y < H) ? depth0[(size_t)p * hw + (unsigned)(y * W + x)] : 0.;
+    }
+    tile_tables(c, s_qx, s_qy);
+    if (x >= W) return;
+    const double qx = s_qx[lx];
+#pragma unroll
+    for (int k = 0; k < SC_PPT; k++) {
+        const int y = blockIdx.y * RT_H + ly + k * RT_ROWS;
+        if (y >= H) break;
+        double d1;
+        const int t = warp_target_n(c, qx, s_qy[ly + k * RT_ROWS], d0[k], H, W, d1);
+        if (t >= 0) atomicMax(winner + (size_t)p * hw + t, (unsigned int)(y * W + x) + 1u);
+    }
 }
 
 __global__ void __launch_bounds__(TPB) age_gather_kernel(const uint64_t *__restrict__ age0,
@@ -223,20 +233,35 @@ __global__ void __launch_bounds__(TPB, SCATTER_MIN_CTAS) prop_scatter_kernel(con
     const int p = blockIdx.z;
     const int hw = H * W;
     const FrameConst c = load_frame_const(T10, cam0, cam1, p);
-    int x, y;
-    double qx, qy, d1;
-    if (!tile_source(c, H, W, s_qx, s_qy, x, y, qx, qy)) return;
-    const unsigned int src = (unsigned int)(y * W + x);
-    const size_t s = (size_t)p * hw + src;
-    const double d0 = depth0[s];
-    const int t = warp_target_n(c, qx, qy, d0, H, W, d1);
-    if (t < 0) return;
-    // what this source carries to its target: propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
-    const double ratio = tdk::inv(d1) / tdk::inv(d0);
-    const double r2 = ratio * ratio;
-    src_d1[s] = d1;
-    src_v1[s] = (r2 * r2) * variance0[s] + bias;
-    next[s] = atomicExch(head + (size_t)p * hw + t, src + 1u);   // 0 terminates a list
+    const int lx = threadIdx.x & (RT_W - 1), ly = threadIdx.x / RT_W;
+    const int x = blockIdx.x * RT_W + lx;
+    double d0[SC_PPT], v0[SC_PPT];
+#pragma unroll
+    for (int k = 0; k < SC_PPT; k++) {   // every map load of the thread is in flight before the tables are built
+        const int y = blockIdx.y * RT_H + ly + k * RT_ROWS;
+        const bool in = x < W && y < H;
+        d0[k] = in ? depth0[(size_t)p * hw + (unsigned)(y * W + x)] : 0.;
+        v0[k] = in ? variance0[(size_t)p * hw + (unsigned)(y * W + x)] : 0.;
+    }
+    tile_tables(c, s_qx, s_qy);
+    if (x >= W) return;
+    const double qx = s_qx[lx];
+#pragma unroll
+    for (int k = 0; k < SC_PPT; k++) {
+        const int y = blockIdx.y * RT_H + ly + k * RT_ROWS;
+        if (y >= H) break;
+        const unsigned int src = (unsigned int)(y * W + x);
+        const size_t s = (size_t)p * hw + src;
+        double d1;
+        const int t = warp_target_n(c, qx, s_qy[ly + k * RT_ROWS], d0[k], H, W, d1);
+        if (t < 0) continue;
+        // what this source carries to its target: propagate_variance, propagation.rs:9-19 ; powi(4) = (r*r)*(r*r)
+        const double ratio = tdk::inv(d1) / tdk::inv(d0[k]);
+        const double r2 = ratio * ratio;
+        src_d1[s] = d1;
+        src_v1[s] = (r2 * r2) * v0[k] + bias;
+        next[s] = atomicExch(head + (size_t)p * hw + t, src + 1u);   // 0 terminates a list
+    }
 }
 
 // handle_collision(a = new, b = stored), propagation.rs:21-46 ; stat.rs:5-26 ; fusion.rs:3-11
