@@ -170,7 +170,11 @@ int tdk_set_kernel_plan(int plan);
 int tdk_set_subpixel_refinement(int on);
 
 /* Host-pointer form: what a numpy caller of the reference binds.  Copies in, runs, copies out,
- * checks the status.  Host buffers may be pageable or pinned. */
+ * checks the status.  Host buffers may be pageable or pinned: the call works in chunks of keyframes
+ * (about 96 MB of input each, three in flight on their own streams) so that uploads, kernels and
+ * read-backs of different chunks overlap -- with PINNED buffers (cudaHostAlloc / cudaHostRegister);
+ * copies from pageable memory are staged by the driver and serialise with the calling thread.
+ * Calls on different devices do not block each other; calls on one device are serialised. */
 int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const double *T_wk,
                           const double *ref_imgs, const double *ref_cams, const double *T_wr,
                           const uint64_t *age, const double *prior_depth,

@@ -31,13 +31,23 @@ int tdk_check_cuda(cudaError_t e, const char *what)
 
 namespace {
 
-constexpr int NSTREAM = 3;
+// Chunking of the host-pointer entry points (measured on the C2 step, PCIe 5 x16):
+//  tdk_update_depth_host         -- H2D dominated (every keyframe ships 8 references): 96 MB chunks in 3 slots
+//                                   (36.0 ms per step; 38.2 with 24-48 MB chunks in 6-8 slots)
+//  tdk_update_depth_frames_host  -- both directions busy: 24 MB chunks (one VGA keyframe) in 6 slots
+//                                   (15.0 ms; 15.2 at 48 MB, 16.0 at 96 MB in 3 slots, 17.5 at 192 MB in 2)
+constexpr int NSTREAM = 6;
+constexpr int HOST_SLOTS = 3;
+constexpr size_t HOST_CHUNK_BYTES = (size_t)96 << 20;
+constexpr int FRAMES_SLOTS = 6;
+constexpr size_t FRAMES_CHUNK_BYTES = (size_t)24 << 20;
 constexpr int MAX_DEV = 64;
 
 struct Arena {
     void *base = nullptr;
     size_t bytes = 0;
-    cudaStream_t streams[NSTREAM] = {nullptr, nullptr, nullptr};
+    cudaStream_t streams[NSTREAM] = {};
+    cudaStream_t upload = nullptr;   // images of tdk_update_depth_frames_host: never queued behind a chunk's read-back
     bool streams_ready = false;
     int *status_host = nullptr;      // pinned, grow-only: the status words of every chunk of a call
     size_t status_words = 0;
@@ -87,6 +97,7 @@ int arena_get(size_t bytes, Arena **out)
     Arena &ar = g_arena[dev];
     if (!ar.streams_ready) {
         for (int i = 0; i < NSTREAM; i++) TDK_CUDA(cudaStreamCreateWithFlags(&ar.streams[i], cudaStreamNonBlocking));
+        TDK_CUDA(cudaStreamCreateWithFlags(&ar.upload, cudaStreamNonBlocking));
         ar.streams_ready = true;
     }
     if (ar.bytes < bytes) {
@@ -166,10 +177,10 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
     const size_t hw = (size_t)H * W;
     // chunk = as many keyframes as fit ~96 MB of staged input, so copies and kernels overlap
     const size_t in_per_key = (size_t)(1 + R + 3) * hw * 8;
-    int64_t C = (int64_t)((96u << 20) / in_per_key);
+    int64_t C = (int64_t)(HOST_CHUNK_BYTES / in_per_key);
     if (C < 1) C = 1;
     if (C > P) C = P;
-    const int nslots = (int)((P + C - 1) / C < NSTREAM ? (P + C - 1) / C : NSTREAM);
+    const int nslots = (int)((P + C - 1) / C < HOST_SLOTS ? (P + C - 1) / C : HOST_SLOTS);
     const size_t slot_bytes = carve_slot(nullptr, 0, C, R, H, W, dbg_argmin != nullptr, out_hist != nullptr, nullptr);
     Arena *ar = nullptr;
     rc = arena_get(slot_bytes * nslots, &ar);
@@ -288,12 +299,12 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
         }
     }
     const int64_t U = (int64_t)unique.size();
-    // chunk = keyframes whose maps (3 in, 3 out) make up ~96 MB
-    int64_t C = (int64_t)((96u << 20) / (6 * hw * 8));
+    // chunk = keyframes whose maps (3 in, 3 out) make up ~24 MB
+    int64_t C = (int64_t)(FRAMES_CHUNK_BYTES / (6 * hw * 8));
     if (C < 1) C = 1;
     if (C > P) C = P;
     const int64_t nchunks = (P + C - 1) / C;
-    const int nslots = (int)(nchunks < NSTREAM ? nchunks : NSTREAM);
+    const int nslots = (int)(nchunks < FRAMES_SLOTS ? nchunks : FRAMES_SLOTS);
     struct FSlot { double *cams, *T_wk, *ref_cams, *T_wr, *pd, *pv, *od, *ov; uint64_t *age; int64_t *of; int32_t *dbg; uint64_t *hist; void *ws; size_t ws_bytes; };
     auto carve = [&](char *base, size_t off, FSlot *f) {
         auto take = [&](size_t bytes) { char *q = base ? base + off : nullptr; off += up256(bytes); return q; };
@@ -326,7 +337,7 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
     int(*st_host)[TDK_ST_WORDS] = reinterpret_cast<int(*)[TDK_ST_WORDS]>(ar->status_host);
     std::vector<char> uploaded((size_t)U, 0);
     std::vector<const double *> kp((size_t)C), rp((size_t)(C * R));
-    cudaStream_t up_stream = ar->streams[0];
+    cudaStream_t up_stream = ar->upload;
     rc = TDK_OK;
 #define GO(call, what) if (rc == TDK_OK) rc = tdk_check_cuda((call), what)
     for (int64_t c = 0; c < nchunks && rc == TDK_OK; c++) {
@@ -345,7 +356,7 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
             for (int64_t r = 0; r < R; r++) rp[i * R + r] = need(ref_slot[(p0 + i) * R + r]);
         }
         GO(cudaEventRecord(ar->events[c], up_stream), "cudaEventRecord");
-        if (st != up_stream) GO(cudaStreamWaitEvent(st, ar->events[c], 0), "cudaStreamWaitEvent");
+        GO(cudaStreamWaitEvent(st, ar->events[c], 0), "cudaStreamWaitEvent");
         GO(cudaMemcpyAsync(f.cams, key_cams + p0 * 4, n * 4 * 8, cudaMemcpyHostToDevice, st), "H2D key_cams");
         GO(cudaMemcpyAsync(f.T_wk, T_wk + p0 * 16, n * 16 * 8, cudaMemcpyHostToDevice, st), "H2D T_wk");
         GO(cudaMemcpyAsync(f.ref_cams, ref_cams + p0 * R * 4, n * R * 4 * 8, cudaMemcpyHostToDevice, st), "H2D ref_cams");
@@ -366,8 +377,8 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
         GO(cudaMemcpyAsync(st_host[c], f.ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, st), "D2H status");
     }
 #undef GO
-    for (int i = 0; i < NSTREAM; i++) {
-        const int rc2 = tdk_check_cuda(cudaStreamSynchronize(ar->streams[i]), "cudaStreamSynchronize");
+    for (int i = 0; i <= NSTREAM; i++) {
+        const int rc2 = tdk_check_cuda(cudaStreamSynchronize(i < NSTREAM ? ar->streams[i] : up_stream), "cudaStreamSynchronize");
         if (rc == TDK_OK) rc = rc2;
     }
     if (rc == TDK_OK) rc = status_report(st_host, nchunks);
