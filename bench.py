@@ -645,10 +645,13 @@ def run_b200(args, rank, world, local_rank):
     e2e_s = time.perf_counter() - t0
     barrier()
     small = sum(pinned[k].numel() * pinned[k].element_size() for k in ("key_cam", "T_wk", "ref_cams", "T_wr"))
-    h2d = nd * (1 + R) * hwb + 3 * B * hwb + small
-    d2h = sum(x.numel() * x.element_size() for x in h_out)
+    # bytes that cross the link: images and f64 maps as they are; the u64 ages and i64 flags of the
+    # caller's arrays travel as one byte per pixel (narrowed / widened by the library's host workers)
+    h2d = nd * (1 + R) * hwb + 2 * B * hwb + B * H * W + small
+    d2h = 2 * B * hwb + B * H * W
     # the e2e path must give the same answer as the resident path
-    same = bool(torch.equal(h_out[0], out[0].cpu()) and torch.equal(h_out[2], out[2].cpu()))
+    same = bool(torch.equal(h_out[0], out[0].cpu()) and torch.equal(h_out[1], out[1].cpu())
+                and torch.equal(h_out[2], out[2].cpu()))
 
     # ---- aggregate over ranks (max time)
     if world > 1:
@@ -701,7 +704,7 @@ def run_b200(args, rank, world, local_rank):
         "e2e": {"value": world * px_step * e2e_steps / e2e_s, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": 1e3 * e2e_s / e2e_steps,
-                "api": "tdk_update_depth_frames_host (pinned host buffers, frames by pointer: the step's "
+                "api": "tdk_update_depth_frames_host (pinned host buffers, u64 ages and i64 flags cross the link as bytes, frames by pointer: the step's "
                        f"{nd * (1 + R)} distinct images cross PCIe once, fuse_on_success=1)",
                 "private_copies": {"value": world * px_step / e2e_private_s, "ms_per_step": 1e3 * e2e_private_s,
                                    "h2d_bytes_per_step": h2d_private,

@@ -117,6 +117,16 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
                                 double *out_depth, double *out_variance, int64_t *out_flag,
                                 int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success,
                                 void *workspace, size_t workspace_bytes, void *stream);
+/* Same again with the two pointer tables themselves in DEVICE memory (a caller that keeps its
+ * frame ring and its tables resident: no host -> device copy is left in the call). */
+int tdk_update_depth_tables_dev(const double *const *key_img_ptrs_dev, const double *key_cams,
+                                const double *T_wk, const double *const *ref_img_ptrs_dev,
+                                const double *ref_cams, const double *T_wr, const uint64_t *age,
+                                const double *prior_depth, const double *prior_variance,
+                                const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
+                                double *out_depth, double *out_variance, int64_t *out_flag,
+                                int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success,
+                                void *workspace, size_t workspace_bytes, void *stream);
 
 int tdk_update_depth_status(const void *workspace, void *stream);
 
@@ -187,7 +197,15 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
  * HOST arrays of HOST image pointers ([H,W] f64 each).  An image named more than once -- the
  * reference frames of the reference's own loop, where every new keyframe is matched against the
  * frames before it (examples/semi_dense_vo.py:196-203; src/py/semi_dense.rs:157-187 clones every
- * reference per call) -- is uploaded once per call.  Everything else as tdk_update_depth_host. */
+ * reference per call) -- is uploaded once per call, on a stream of its own, in the order the keyframes
+ * need them; cameras, poses and pointer tables go up once; the maps travel in chunks of about 32 MB
+ * (two VGA keyframes), six in flight, so that both directions of the link stay busy.  For R < 255
+ * the age maps (values <= R; anything larger is reported as TDK_ERR_AGE whatever its value) and the
+ * flag maps (-9 .. 0) cross the link as ONE byte per pixel instead of eight: a small pool of host
+ * threads (TDK_HOST_THREADS, default min(8, hardware threads), created on first use) narrows the
+ * caller's age maps into pinned memory ahead of the uploads and widens the flags into out_flag
+ * behind the read-backs; two small kernels do the opposite on the device.  The arrays the caller
+ * sees keep the reference's u64 / i64 layout.  Everything else as tdk_update_depth_host. */
 int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double *key_cams,
                                  const double *T_wk, const double *const *ref_img_ptrs,
                                  const double *ref_cams, const double *T_wr, const uint64_t *age,

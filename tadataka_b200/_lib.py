@@ -44,6 +44,8 @@ update_depth_dev = _sig("tdk_update_depth_dev", C.c_int, P, P, P, P, P, P, P, P,
                         I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_frames_dev = _sig("tdk_update_depth_frames_dev", C.c_int, P, P, P, P, P, P, P, P, P,
                                P, I64, I64, I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
+update_depth_tables_dev = _sig("tdk_update_depth_tables_dev", C.c_int, P, P, P, P, P, P, P, P, P,
+                               P, I64, I64, I64, I64, P, P, P, P, P, C.c_int, P, SZ, P)
 update_depth_static_dev = _sig("tdk_update_depth_static_dev", C.c_int, P, P, P, P, P, P, P, P, P,
                                P, I64, I64, I64, I64, P, P, P, P, P, C.c_int, C.c_int, P)
 STATIC_MAX_PAIRS = 64
@@ -110,7 +112,7 @@ dvo_tukey_scale_dev = _sig("tdk_dvo_tukey_scale_dev", C.c_int, P, P, P, D, P, P,
 EXPORTS = [
     "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
     "tdk_update_depth_workspace_bytes_min",
-    "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_status",
+    "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_tables_dev", "tdk_update_depth_status",
     "tdk_update_depth_static_dev",
     "tdk_update_depth_host", "tdk_estimate_debug_host", "tdk_fusion_dev", "tdk_regularize_dev",
     "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",

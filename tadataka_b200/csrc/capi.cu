@@ -6,7 +6,13 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -34,13 +40,20 @@ namespace {
 // Chunking of the host-pointer entry points (measured on the C2 step, PCIe 5 x16):
 //  tdk_update_depth_host         -- H2D dominated (every keyframe ships 8 references): 96 MB chunks in 3 slots
 //                                   (36.0 ms per step; 38.2 with 24-48 MB chunks in 6-8 slots)
-//  tdk_update_depth_frames_host  -- both directions busy: 24 MB chunks (one VGA keyframe) in 6 slots
-//                                   (15.0 ms; 15.2 at 48 MB, 16.0 at 96 MB in 3 slots, 17.5 at 192 MB in 2)
-constexpr int NSTREAM = 6;
+//  tdk_update_depth_frames_host  -- both directions busy: 32 MB chunks (two VGA keyframes, 4.9 MB per copy) in 6
+//                                   slots (13.3 ms; 13.9 with one keyframe or with four per chunk, 13.9 in 4 slots;
+//                                   tools/pcie_copy_size.py: 81 GB/s both ways at 2.5 MB per copy, 90 from 4.9 MB on)
+#ifndef TDK_FRAMES_SLOTS
+#define TDK_FRAMES_SLOTS 6
+#endif
+#ifndef TDK_FRAMES_CHUNK_MB
+#define TDK_FRAMES_CHUNK_MB 32
+#endif
+constexpr int NSTREAM = TDK_FRAMES_SLOTS > 6 ? TDK_FRAMES_SLOTS : 6;
 constexpr int HOST_SLOTS = 3;
 constexpr size_t HOST_CHUNK_BYTES = (size_t)96 << 20;
-constexpr int FRAMES_SLOTS = 6;
-constexpr size_t FRAMES_CHUNK_BYTES = (size_t)24 << 20;
+constexpr int FRAMES_SLOTS = TDK_FRAMES_SLOTS;
+constexpr size_t FRAMES_CHUNK_BYTES = (size_t)TDK_FRAMES_CHUNK_MB << 20;
 constexpr int MAX_DEV = 64;
 
 struct Arena {
@@ -51,8 +64,159 @@ struct Arena {
     bool streams_ready = false;
     int *status_host = nullptr;      // pinned, grow-only: the status words of every chunk of a call
     size_t status_words = 0;
-    std::vector<cudaEvent_t> events; // grow-only pool (tdk_update_depth_frames_host: "images of chunk c are up")
+    std::vector<cudaEvent_t> events; // grow-only pool (tdk_update_depth_frames_host: three per chunk)
+    unsigned char *wire_host = nullptr;   // pinned, grow-only: 8-bit age maps going up, 8-bit flag maps coming back
+    size_t wire_bytes = 0;
 };
+
+// ---- host workers of the narrow-wire path (tdk_update_depth_frames_host)
+// The reference's layout spends 8 bytes per pixel on an age (<= R) and 8 on a flag (-9 .. 0).  Over
+// PCIe they travel as one byte each: worker threads narrow the caller's age maps into pinned memory
+// ahead of the uploads and widen the flag maps into the caller's array behind the read-backs; two
+// small kernels do the opposite on the device.  The pool is created on first use and never
+// destroyed (its threads sleep on a condition variable; a heap object, so no static destructor
+// runs under them).  TDK_HOST_THREADS sets its size (default: min(8, hardware threads)).
+class HostPool {
+public:
+    static HostPool &get()
+    {
+        static HostPool *pool = new HostPool;
+        return *pool;
+    }
+    void submit(std::function<void()> fn)
+    {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            q_.push_back(std::move(fn));
+        }
+        cv_.notify_one();
+    }
+
+private:
+    HostPool()
+    {
+        int n = 0;
+        if (const char *e = getenv("TDK_HOST_THREADS")) n = atoi(e);
+        if (n <= 0) {
+            n = (int)std::thread::hardware_concurrency();
+            if (n > 8) n = 8;
+        }
+        if (n < 1) n = 1;
+        for (int i = 0; i < n; i++) std::thread([this] { loop(); }).detach();
+    }
+    void loop()
+    {
+        for (;;) {
+            std::function<void()> fn;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [this] { return !q_.empty(); });
+                fn = std::move(q_.front());
+                q_.pop_front();
+            }
+            fn();
+        }
+    }
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::deque<std::function<void()>> q_;
+};
+
+// what one call's chunks wait on: "chunk c's ages are narrowed", "chunk c's flags are in the caller's array"
+struct ChunkSync {
+    std::mutex m;
+    std::condition_variable cv;
+    std::vector<int> narrow_left, widen_left;   // pieces of chunk c still with the workers; -1 = not handed out yet
+    int64_t pending = 0;                        // pieces handed to the pool and not finished
+    explicit ChunkSync(int64_t n) : narrow_left((size_t)n, -1), widen_left((size_t)n, -1) {}
+    void begin(std::vector<int> &left, int64_t c, int pieces)
+    {
+        std::lock_guard<std::mutex> lk(m);
+        left[(size_t)c] = pieces;
+        pending += pieces;
+    }
+    void end(std::vector<int> &left, int64_t c)
+    {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            left[(size_t)c]--;
+            pending--;
+        }
+        cv.notify_all();
+    }
+    void wait(const std::vector<int> &left, int64_t c)
+    {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return left[(size_t)c] == 0; });
+    }
+    void drain()
+    {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return pending == 0; });
+    }
+};
+
+constexpr size_t HOST_PIECE = 76800;   // pixels per worker task: a chunk's map is converted by several threads
+
+#ifdef TDK_HOST_TIMING
+double host_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+#endif
+
+void narrow_age_host(const uint64_t *src, unsigned char *dst, size_t n)
+{
+    for (size_t i = 0; i < n; i++) dst[i] = src[i] > 255u ? (unsigned char)255 : (unsigned char)src[i];
+}
+
+void widen_flag_host(const signed char *src, int64_t *dst, size_t n)
+{
+    for (size_t i = 0; i < n; i++) dst[i] = src[i];
+}
+
+// device side of the narrow wire; eight values per thread, the tail one by one
+__global__ void __launch_bounds__(256) widen_age_kernel(const unsigned char *__restrict__ in, uint64_t *__restrict__ out,
+                                                         size_t n)
+{
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (i + 8 <= n) {
+        const uint2 v = *reinterpret_cast<const uint2 *>(in + i);
+        ulonglong2 *o = reinterpret_cast<ulonglong2 *>(out + i);
+        o[0] = make_ulonglong2(v.x & 255u, (v.x >> 8) & 255u);
+        o[1] = make_ulonglong2((v.x >> 16) & 255u, v.x >> 24);
+        o[2] = make_ulonglong2(v.y & 255u, (v.y >> 8) & 255u);
+        o[3] = make_ulonglong2((v.y >> 16) & 255u, v.y >> 24);
+    } else {
+        for (size_t j = i; j < n; j++) out[j] = in[j];
+    }
+}
+
+__global__ void __launch_bounds__(256) narrow_flag_kernel(const int64_t *__restrict__ in, signed char *__restrict__ out,
+                                                           size_t n, const int *__restrict__ status_src,
+                                                           int *__restrict__ status_dst)
+{
+    // the chunk's status words move to the call's table on the way (one read-back per call, not per chunk)
+    if (blockIdx.x == 0 && threadIdx.x < TDK_ST_WORDS) status_dst[threadIdx.x] = status_src[threadIdx.x];
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (i + 8 <= n) {
+        const longlong2 *q = reinterpret_cast<const longlong2 *>(in + i);
+        const longlong2 a = q[0], b = q[1], c = q[2], d = q[3];
+        uint2 v;
+        v.x = ((unsigned)a.x & 255u) | (((unsigned)a.y & 255u) << 8) | (((unsigned)b.x & 255u) << 16) | (((unsigned)b.y & 255u) << 24);
+        v.y = ((unsigned)c.x & 255u) | (((unsigned)c.y & 255u) << 8) | (((unsigned)d.x & 255u) << 16) | (((unsigned)d.y & 255u) << 24);
+        *reinterpret_cast<uint2 *>(out + i) = v;
+    } else {
+        for (size_t j = i; j < n; j++) out[j] = (signed char)in[j];
+    }
+}
+
+int wire_host_get(Arena *ar, size_t bytes)
+{
+    if (ar->wire_bytes < bytes) {
+        if (ar->wire_host) { TDK_CUDA(cudaFreeHost(ar->wire_host)); ar->wire_host = nullptr; ar->wire_bytes = 0; }
+        TDK_CUDA(cudaMallocHost((void **)&ar->wire_host, bytes));
+        ar->wire_bytes = bytes;
+    }
+    return TDK_OK;
+}
 
 int status_host_get(Arena *ar, int64_t nchunks)
 {
@@ -299,20 +463,22 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
         }
     }
     const int64_t U = (int64_t)unique.size();
-    // chunk = keyframes whose maps (3 in, 3 out) make up ~24 MB
+    // chunk = keyframes whose maps (3 in, 3 out) make up ~32 MB
     int64_t C = (int64_t)(FRAMES_CHUNK_BYTES / (6 * hw * 8));
     if (C < 1) C = 1;
     if (C > P) C = P;
     const int64_t nchunks = (P + C - 1) / C;
     const int nslots = (int)(nchunks < FRAMES_SLOTS ? nchunks : FRAMES_SLOTS);
-    struct FSlot { double *cams, *T_wk, *ref_cams, *T_wr, *pd, *pv, *od, *ov; uint64_t *age; int64_t *of; int32_t *dbg; uint64_t *hist; void *ws; size_t ws_bytes; };
+    // ages (<= R, anything larger is an error whatever its value) and flags (-9 .. 0) cross the link as bytes
+    const bool narrow = R < 255;
+    struct FSlot { double *pd, *pv, *od, *ov; uint64_t *age; int64_t *of; unsigned char *age8; signed char *of8; int32_t *dbg; uint64_t *hist; void *ws; size_t ws_bytes; };
     auto carve = [&](char *base, size_t off, FSlot *f) {
         auto take = [&](size_t bytes) { char *q = base ? base + off : nullptr; off += up256(bytes); return q; };
         FSlot t;
-        t.cams = (double *)take(C * 4 * 8); t.T_wk = (double *)take(C * 16 * 8);
-        t.ref_cams = (double *)take(C * R * 4 * 8); t.T_wr = (double *)take(C * R * 16 * 8);
         t.age = (uint64_t *)take(C * hw * 8); t.pd = (double *)take(C * hw * 8); t.pv = (double *)take(C * hw * 8);
         t.od = (double *)take(C * hw * 8); t.ov = (double *)take(C * hw * 8); t.of = (int64_t *)take(C * hw * 8);
+        t.age8 = narrow ? (unsigned char *)take(C * hw) : nullptr;
+        t.of8 = narrow ? (signed char *)take(C * hw) : nullptr;
         t.dbg = dbg_argmin ? (int32_t *)take(C * hw * 4) : nullptr;
         t.hist = out_hist ? (uint64_t *)take(C * 10 * 8) : nullptr;
         t.ws_bytes = tdk_update_depth_workspace_bytes(C, R, H, W);
@@ -322,65 +488,175 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
     };
     const size_t img_bytes = up256((size_t)U * hw * 8);
     const size_t slot_bytes = carve(nullptr, 0, nullptr);
+    // what the whole call needs once: cameras, poses, the two tables of device image pointers, a status row per chunk
+    struct Tables { double *cams, *T_wk, *ref_cams, *T_wr; const double **kptr, **rptr; int *status; } tab;
+    auto carve_tables = [&](char *base, size_t off) {
+        auto take = [&](size_t bytes) { char *q = base ? base + off : nullptr; off += up256(bytes); return q; };
+        tab.cams = (double *)take(P * 4 * 8); tab.T_wk = (double *)take(P * 16 * 8);
+        tab.ref_cams = (double *)take(P * R * 4 * 8); tab.T_wr = (double *)take(P * R * 16 * 8);
+        tab.kptr = (const double **)take(P * sizeof(void *)); tab.rptr = (const double **)take(P * R * sizeof(void *));
+        tab.status = (int *)take(nchunks * TDK_ST_WORDS * sizeof(int));
+        return off;
+    };
+    const size_t tab_bytes = carve_tables(nullptr, 0);
     Arena *ar = nullptr;
-    rc = arena_get(img_bytes + slot_bytes * nslots, &ar);
+    rc = arena_get(img_bytes + tab_bytes + slot_bytes * nslots, &ar);
     if (rc != TDK_OK) return rc;
     if ((rc = status_host_get(ar, nchunks)) != TDK_OK) return rc;
-    while ((int64_t)ar->events.size() < nchunks) {
+    // events per chunk: [c] its images are up, [nchunks + c] its ages are up, [2 nchunks + c] its results are down
+    while ((int64_t)ar->events.size() < 3 * nchunks) {
         cudaEvent_t e;
         TDK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ar->events.push_back(e);
     }
+    cudaEvent_t *ev_img = ar->events.data(), *ev_in = ev_img + nchunks, *ev_out = ev_in + nchunks;
+    // pinned byte maps: a ring of RING chunks each way; a slot is taken again only when its last user is through
+    const int64_t RING = nchunks < 64 ? nchunks : 64;
+    const int64_t AHEAD = RING < 16 ? RING : 16;           // chunks the narrowing runs ahead of the uploads
+    const size_t wire_chunk = up256((size_t)C * hw);
+    unsigned char *age_wire = nullptr;
+    signed char *flag_wire = nullptr;
+    if (narrow) {
+        if ((rc = wire_host_get(ar, 2 * wire_chunk * (size_t)RING)) != TDK_OK) return rc;
+        age_wire = ar->wire_host;
+        flag_wire = (signed char *)(ar->wire_host + wire_chunk * (size_t)RING);
+    }
     double *images = (double *)ar->base;
     FSlot slots[NSTREAM];
-    for (int i = 0; i < nslots; i++) carve((char *)ar->base, img_bytes + slot_bytes * i, &slots[i]);
+    carve_tables((char *)ar->base, img_bytes);
+    for (int i = 0; i < nslots; i++) carve((char *)ar->base, img_bytes + tab_bytes + slot_bytes * i, &slots[i]);
     int(*st_host)[TDK_ST_WORDS] = reinterpret_cast<int(*)[TDK_ST_WORDS]>(ar->status_host);
     std::vector<char> uploaded((size_t)U, 0);
-    std::vector<const double *> kp((size_t)C), rp((size_t)(C * R));
+    std::vector<const double *> kp((size_t)P), rp((size_t)(P * R));   // device addresses of every keyframe's images
+    for (int64_t i = 0; i < P; i++) kp[i] = images + (size_t)key_slot[i] * hw;
+    for (int64_t i = 0; i < P * R; i++) rp[i] = images + (size_t)ref_slot[i] * hw;
     cudaStream_t up_stream = ar->upload;
+#ifdef TDK_HOST_TIMING
+    const double t_begin = host_now();
+#endif
+    ChunkSync sync(nchunks);
+    auto chunk_len = [&](int64_t c) { return (c * C + C <= P) ? C : P - c * C; };
     rc = TDK_OK;
 #define GO(call, what) if (rc == TDK_OK) rc = tdk_check_cuda((call), what)
+    // the upload stream carries the tables first, then the images in the order the chunks need them
+    GO(cudaMemcpyAsync(tab.cams, key_cams, P * 4 * 8, cudaMemcpyHostToDevice, up_stream), "H2D key_cams");
+    GO(cudaMemcpyAsync(tab.T_wk, T_wk, P * 16 * 8, cudaMemcpyHostToDevice, up_stream), "H2D T_wk");
+    GO(cudaMemcpyAsync(tab.ref_cams, ref_cams, P * R * 4 * 8, cudaMemcpyHostToDevice, up_stream), "H2D ref_cams");
+    GO(cudaMemcpyAsync(tab.T_wr, T_wr, P * R * 16 * 8, cudaMemcpyHostToDevice, up_stream), "H2D T_wr");
+    GO(cudaMemcpyAsync(tab.kptr, kp.data(), P * sizeof(void *), cudaMemcpyHostToDevice, up_stream), "H2D key pointers");
+    GO(cudaMemcpyAsync(tab.rptr, rp.data(), P * R * sizeof(void *), cudaMemcpyHostToDevice, up_stream), "H2D ref pointers");
+    int64_t next_narrow = 0, next_widen = 0;
+    // hand chunk k's age maps to the workers (its ring slot is free once chunk k - RING has been uploaded)
+    auto narrow_upto = [&](int64_t upto) {
+        for (; narrow && next_narrow < nchunks && next_narrow < upto && rc == TDK_OK; next_narrow++) {
+            const int64_t k = next_narrow;
+            if (k >= RING) GO(cudaEventSynchronize(ev_in[k - RING]), "cudaEventSynchronize");
+            if (rc != TDK_OK) break;
+            const uint64_t *src = age + (size_t)k * C * hw;
+            unsigned char *dst = age_wire + wire_chunk * (size_t)(k % RING);
+            const size_t cnt = (size_t)chunk_len(k) * hw;
+            const int pieces = (int)((cnt + HOST_PIECE - 1) / HOST_PIECE);
+            sync.begin(sync.narrow_left, k, pieces);
+            for (size_t o = 0; o < cnt; o += HOST_PIECE) {
+                const size_t len = cnt - o < HOST_PIECE ? cnt - o : HOST_PIECE;
+                HostPool::get().submit([src, dst, o, len, k, &sync] { narrow_age_host(src + o, dst + o, len); sync.end(sync.narrow_left, k); });
+            }
+        }
+    };
+    // wait for chunk k's read-back and hand its flag map to the workers
+    auto widen_upto = [&](int64_t upto) {
+        for (; narrow && next_widen < upto && rc == TDK_OK; next_widen++) {
+            const int64_t k = next_widen;
+            GO(cudaEventSynchronize(ev_out[k]), "cudaEventSynchronize");
+            if (rc != TDK_OK) break;
+            const signed char *src = flag_wire + wire_chunk * (size_t)(k % RING);
+            int64_t *dst = out_flag + (size_t)k * C * hw;
+            const size_t cnt = (size_t)chunk_len(k) * hw;
+            const int pieces = (int)((cnt + HOST_PIECE - 1) / HOST_PIECE);
+            sync.begin(sync.widen_left, k, pieces);
+            for (size_t o = 0; o < cnt; o += HOST_PIECE) {
+                const size_t len = cnt - o < HOST_PIECE ? cnt - o : HOST_PIECE;
+                HostPool::get().submit([src, dst, o, len, k, &sync] { widen_flag_host(src + o, dst + o, len); sync.end(sync.widen_left, k); });
+            }
+        }
+    };
     for (int64_t c = 0; c < nchunks && rc == TDK_OK; c++) {
-        const int64_t p0 = c * C, n = (p0 + C <= P) ? C : P - p0;
+        const int64_t p0 = c * C, n = chunk_len(c);
         FSlot &f = slots[c % nslots];
         cudaStream_t st = ar->streams[c % nslots];
+        if (narrow && c >= RING) {   // the flag ring comes round: chunk c - RING must have left its slot
+            widen_upto(c - RING + 1);
+            if (rc == TDK_OK) sync.wait(sync.widen_left, c - RING);
+        }
+        narrow_upto(c + AHEAD + 1);
         auto need = [&](int64_t u) {
             if (!uploaded[u]) {
                 GO(cudaMemcpyAsync(images + (size_t)u * hw, unique[u], hw * 8, cudaMemcpyHostToDevice, up_stream), "H2D image");
                 uploaded[u] = 1;
             }
-            return (const double *)(images + (size_t)u * hw);
         };
         for (int64_t i = 0; i < n; i++) {
-            kp[i] = need(key_slot[p0 + i]);
-            for (int64_t r = 0; r < R; r++) rp[i * R + r] = need(ref_slot[(p0 + i) * R + r]);
+            need(key_slot[p0 + i]);
+            for (int64_t r = 0; r < R; r++) need(ref_slot[(p0 + i) * R + r]);
         }
-        GO(cudaEventRecord(ar->events[c], up_stream), "cudaEventRecord");
-        GO(cudaStreamWaitEvent(st, ar->events[c], 0), "cudaStreamWaitEvent");
-        GO(cudaMemcpyAsync(f.cams, key_cams + p0 * 4, n * 4 * 8, cudaMemcpyHostToDevice, st), "H2D key_cams");
-        GO(cudaMemcpyAsync(f.T_wk, T_wk + p0 * 16, n * 16 * 8, cudaMemcpyHostToDevice, st), "H2D T_wk");
-        GO(cudaMemcpyAsync(f.ref_cams, ref_cams + p0 * R * 4, n * R * 4 * 8, cudaMemcpyHostToDevice, st), "H2D ref_cams");
-        GO(cudaMemcpyAsync(f.T_wr, T_wr + p0 * R * 16, n * R * 16 * 8, cudaMemcpyHostToDevice, st), "H2D T_wr");
-        GO(cudaMemcpyAsync(f.age, age + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D age");
-        GO(cudaMemcpyAsync(f.pd, prior_depth + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D prior_depth");
-        GO(cudaMemcpyAsync(f.pv, prior_variance + p0 * hw, n * hw * 8, cudaMemcpyHostToDevice, st), "H2D prior_variance");
+        GO(cudaEventRecord(ev_img[c], up_stream), "cudaEventRecord");
+        GO(cudaStreamWaitEvent(st, ev_img[c], 0), "cudaStreamWaitEvent");
+        const size_t cnt = (size_t)n * hw;
+        const unsigned blocks = (unsigned)((cnt + 2047) / 2048);
+        // the two f64 maps first: the widening kernel then runs while they are still on the way in other streams
+        GO(cudaMemcpyAsync(f.pd, prior_depth + p0 * hw, cnt * 8, cudaMemcpyHostToDevice, st), "H2D prior_depth");
+        GO(cudaMemcpyAsync(f.pv, prior_variance + p0 * hw, cnt * 8, cudaMemcpyHostToDevice, st), "H2D prior_variance");
+        if (narrow) {
+            if (rc == TDK_OK) sync.wait(sync.narrow_left, c);
+            GO(cudaMemcpyAsync(f.age8, age_wire + wire_chunk * (size_t)(c % RING), cnt, cudaMemcpyHostToDevice, st), "H2D age");
+            GO(cudaEventRecord(ev_in[c], st), "cudaEventRecord");
+            if (rc == TDK_OK) {
+                widen_age_kernel<<<blocks, 256, 0, st>>>(f.age8, f.age, cnt);
+                rc = tdk_check_cuda(cudaGetLastError(), "widen_age_kernel");
+            }
+        } else {
+            GO(cudaMemcpyAsync(f.age, age + p0 * hw, cnt * 8, cudaMemcpyHostToDevice, st), "H2D age");
+        }
         if (f.hist) GO(cudaMemsetAsync(f.hist, 0, n * 10 * 8, st), "memset hist");
         if (rc == TDK_OK)
-            rc = tdk_update_depth_frames_dev(kp.data(), f.cams, f.T_wk, rp.data(), f.ref_cams, f.T_wr, f.age, f.pd, f.pv,
+            rc = tdk_update_depth_tables_dev(tab.kptr + p0, tab.cams + p0 * 4, tab.T_wk + p0 * 16, tab.rptr + p0 * R,
+                                             tab.ref_cams + p0 * R * 4, tab.T_wr + p0 * R * 16, f.age, f.pd, f.pv,
                                              params, n, R, H, W, f.od, f.ov, f.of, f.dbg, f.hist, fuse_on_success, f.ws,
                                              f.ws_bytes, st);
-        GO(cudaMemcpyAsync(out_depth + p0 * hw, f.od, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H depth");
-        GO(cudaMemcpyAsync(out_variance + p0 * hw, f.ov, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H variance");
-        GO(cudaMemcpyAsync(out_flag + p0 * hw, f.of, n * hw * 8, cudaMemcpyDeviceToHost, st), "D2H flag");
-        if (dbg_argmin) GO(cudaMemcpyAsync(dbg_argmin + p0 * hw, f.dbg, n * hw * 4, cudaMemcpyDeviceToHost, st), "D2H argmin");
+        if (narrow && rc == TDK_OK) {
+            narrow_flag_kernel<<<blocks, 256, 0, st>>>(f.of, f.of8, cnt, (const int *)f.ws, tab.status + c * TDK_ST_WORDS);
+            rc = tdk_check_cuda(cudaGetLastError(), "narrow_flag_kernel");
+        }
+        GO(cudaMemcpyAsync(out_depth + p0 * hw, f.od, cnt * 8, cudaMemcpyDeviceToHost, st), "D2H depth");
+        GO(cudaMemcpyAsync(out_variance + p0 * hw, f.ov, cnt * 8, cudaMemcpyDeviceToHost, st), "D2H variance");
+        if (narrow)
+            GO(cudaMemcpyAsync(flag_wire + wire_chunk * (size_t)(c % RING), f.of8, cnt, cudaMemcpyDeviceToHost, st), "D2H flag");
+        else
+            GO(cudaMemcpyAsync(out_flag + p0 * hw, f.of, cnt * 8, cudaMemcpyDeviceToHost, st), "D2H flag");
+        if (dbg_argmin) GO(cudaMemcpyAsync(dbg_argmin + p0 * hw, f.dbg, cnt * 4, cudaMemcpyDeviceToHost, st), "D2H argmin");
         if (out_hist) GO(cudaMemcpyAsync(out_hist + p0 * 10, f.hist, n * 10 * 8, cudaMemcpyDeviceToHost, st), "D2H hist");
-        GO(cudaMemcpyAsync(st_host[c], f.ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, st), "D2H status");
+        if (!narrow) GO(cudaMemcpyAsync(st_host[c], f.ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, st), "D2H status");
+        GO(cudaEventRecord(ev_out[c], st), "cudaEventRecord");
     }
+#ifdef TDK_HOST_TIMING
+    const double t_enq = host_now();
+#endif
+    widen_upto(nchunks);
 #undef GO
+#ifdef TDK_HOST_TIMING
+    const double t_wid = host_now();
+#endif
+    sync.drain();   // no worker may still hold a pointer into this frame or the caller's arrays
     for (int i = 0; i <= NSTREAM; i++) {
         const int rc2 = tdk_check_cuda(cudaStreamSynchronize(i < NSTREAM ? ar->streams[i] : up_stream), "cudaStreamSynchronize");
         if (rc == TDK_OK) rc = rc2;
     }
+    if (narrow && rc == TDK_OK)
+        rc = tdk_check_cuda(cudaMemcpy(st_host, tab.status, sizeof(int) * TDK_ST_WORDS * nchunks, cudaMemcpyDeviceToHost), "D2H status");
+#ifdef TDK_HOST_TIMING
+    fprintf(stderr, "frames_host: enqueue %.2f ms, read-backs done +%.2f ms, end +%.2f ms (%lld chunks)\n",
+            1e3 * (t_enq - t_begin), 1e3 * (t_wid - t_enq), 1e3 * (host_now() - t_wid), (long long)nchunks);
+#endif
     if (rc == TDK_OK) rc = status_report(st_host, nchunks);
     return rc;
 }

@@ -1457,7 +1457,7 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
            const double *prior_variance, const double *params, int64_t P, int64_t R, int64_t H,
            int64_t W, double *out_depth, double *out_variance, int64_t *out_flag, int32_t *dbg_argmin,
            uint64_t *out_hist, int fuse, int plan, void *workspace, size_t workspace_bytes,
-           cudaStream_t stream)
+           cudaStream_t stream, bool tables_on_device = false)
 {
     TdkRange range("tdk_update_depth");
     if (!key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth || !prior_variance ||
@@ -1525,15 +1525,20 @@ int launch(const double *key_imgs, const double *const *key_ptrs_host, const dou
     TdkPairConst *pairs = (TdkPairConst *)(ws + l.pairs);
     const double *const *key_ptrs = nullptr, *const *ref_ptrs = nullptr;
     TDK_CUDA(cudaMemsetAsync(status, 0, TDK_ST_WORDS * sizeof(int), stream));
-    if (key_ptrs_host) {
-        TDK_CUDA(cudaMemcpyAsync(ws + l.key_ptrs, key_ptrs_host, (size_t)P * sizeof(void *),
-                                 cudaMemcpyHostToDevice, stream));
-        key_ptrs = (const double *const *)(ws + l.key_ptrs);
-    }
-    if (ref_ptrs_host) {
-        TDK_CUDA(cudaMemcpyAsync(ws + l.ref_ptrs, ref_ptrs_host, (size_t)P * R * sizeof(void *),
-                                 cudaMemcpyHostToDevice, stream));
-        ref_ptrs = (const double *const *)(ws + l.ref_ptrs);
+    if (tables_on_device) {   // the caller's tables are device memory already
+        key_ptrs = key_ptrs_host;
+        ref_ptrs = ref_ptrs_host;
+    } else {
+        if (key_ptrs_host) {
+            TDK_CUDA(cudaMemcpyAsync(ws + l.key_ptrs, key_ptrs_host, (size_t)P * sizeof(void *),
+                                     cudaMemcpyHostToDevice, stream));
+            key_ptrs = (const double *const *)(ws + l.key_ptrs);
+        }
+        if (ref_ptrs_host) {
+            TDK_CUDA(cudaMemcpyAsync(ws + l.ref_ptrs, ref_ptrs_host, (size_t)P * R * sizeof(void *),
+                                     cudaMemcpyHostToDevice, stream));
+            ref_ptrs = (const double *const *)(ws + l.ref_ptrs);
+        }
     }
     const int npairs = (int)(P * R);
     const size_t counter_words = (size_t)l.sub * COUNTER_WORDS;
@@ -1758,6 +1763,25 @@ int tdk_update_depth_frames_dev(const double *const *key_img_ptrs, const double 
                   prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
                   dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan.load(), P, H, W), workspace, workspace_bytes,
                   (cudaStream_t)stream);
+}
+
+int tdk_update_depth_tables_dev(const double *const *key_img_ptrs_dev, const double *key_cams,
+                                const double *T_wk, const double *const *ref_img_ptrs_dev,
+                                const double *ref_cams, const double *T_wr, const uint64_t *age,
+                                const double *prior_depth, const double *prior_variance,
+                                const double *params, int64_t P, int64_t R, int64_t H, int64_t W,
+                                double *out_depth, double *out_variance, int64_t *out_flag,
+                                int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success,
+                                void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (!key_img_ptrs_dev || !ref_img_ptrs_dev) {
+        tdk_set_error("tdk_update_depth_tables_dev: null pointer table");
+        return TDK_ERR_INVALID;
+    }
+    return launch(nullptr, key_img_ptrs_dev, key_cams, T_wk, nullptr, ref_img_ptrs_dev, ref_cams, T_wr, age,
+                  prior_depth, prior_variance, params, P, R, H, W, out_depth, out_variance, out_flag,
+                  dbg_argmin, out_hist, fuse_on_success, resolve_plan(g_plan.load(), P, H, W), workspace, workspace_bytes,
+                  (cudaStream_t)stream, true);
 }
 
 int tdk_update_depth_status(const void *workspace, void *stream)

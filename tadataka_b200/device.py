@@ -127,10 +127,11 @@ def update_depth(key_imgs, key_cams, T_wk, ref_imgs, ref_cams, T_wr, age, prior_
 
 
 def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, prior_depth,
-                        prior_variance, params, debug=False, fuse=False):
+                        prior_variance, params, debug=False, fuse=False, device_tables=False):
     """One keyframe against a list of separately allocated reference images (a device-resident
     keyframe ring).  key_img [H,W]; ref_imgs: list of R tensors [H,W]; ref_cams [R,4];
-    T_wr [R,4,4]; maps [H,W].  Returns (depth, variance, flag[, argmin]) as [H,W] tensors."""
+    T_wr [R,4,4]; maps [H,W].  Returns (depth, variance, flag[, argmin]) as [H,W] tensors.
+    device_tables: hand the image pointers over as a device array (tdk_update_depth_tables_dev)."""
     _require_cuda()
     _chk(key_img, "key_img", _F64)
     H, W = key_img.shape
@@ -156,11 +157,16 @@ def update_depth_frames(key_img, key_cam, T_wk, ref_imgs, ref_cams, T_wr, age, p
         kp = (C.c_void_p * 1)(key_img.data_ptr())
         rp = (C.c_void_p * R)(*[r.data_ptr() for r in ref_imgs])
         ws = workspace(_lib.update_depth_workspace_bytes(1, R, H, W), dev, "update_depth")
-        rc = _lib.update_depth_frames_dev(kp, _ptr(key_cam), _ptr(T_wk), rp, _ptr(ref_cams),
-                                          _ptr(T_wr), _ptr(age), _ptr(prior_depth),
-                                          _ptr(prior_variance), pa.ctypes.data_as(C.c_void_p), 1, R,
-                                          H, W, _ptr(od), _ptr(ov), _ptr(of), _ptr(dbg), None,
-                                          int(bool(fuse)), _ptr(ws), ws.numel(), _stream())
+        entry = _lib.update_depth_frames_dev
+        if device_tables:
+            table = torch.tensor([key_img.data_ptr()] + [r.data_ptr() for r in ref_imgs], dtype=torch.int64, device=dev)
+            kp, rp = C.c_void_p(table.data_ptr()), C.c_void_p(table.data_ptr() + 8)
+            entry = _lib.update_depth_tables_dev
+        rc = entry(kp, _ptr(key_cam), _ptr(T_wk), rp, _ptr(ref_cams),
+                   _ptr(T_wr), _ptr(age), _ptr(prior_depth),
+                   _ptr(prior_variance), pa.ctypes.data_as(C.c_void_p), 1, R,
+                   H, W, _ptr(od), _ptr(ov), _ptr(of), _ptr(dbg), None,
+                   int(bool(fuse)), _ptr(ws), ws.numel(), _stream())
         _lib.check(rc)
         # the pointer tables are copied with cudaMemcpyAsync from these host arrays: the status
         # read below synchronises the stream before they go out of scope

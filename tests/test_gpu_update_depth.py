@@ -305,6 +305,49 @@ def test_host_pointer_entry_point_with_shared_frames():
                                          P, R, H, W, p(od), p(ov), p(of), None, None, 0) == _lib.ERR_INVALID
 
 
+def test_frames_host_byte_wire_ring_and_age_errors():
+    """tdk_update_depth_frames_host moves ages and flags as bytes through a pinned ring of 64
+    chunks: 70 VGA pairs (one keyframe per chunk) make the ring come round.  Same maps as the
+    oracle; an age beyond R is still reported, whether it fits a byte or not."""
+    import ctypes as C
+    from tadataka_b200 import _lib
+    base = [scene.make_pair(770 + i) for i in range(2)]
+    rng = np.random.default_rng(77)
+    items = []
+    for k in range(70):
+        it = dict(base[k % 2])
+        it["prior_variance"] = np.ascontiguousarray(10.0 ** rng.uniform(-3.0, 0.0, size=it["prior_variance"].shape))
+        it["age"] = np.ascontiguousarray((rng.random(it["age"].shape) < 0.9).astype(np.uint64))
+        items.append(it)
+    b = scene.stack_keyframes(items)
+    P, H, W = b["key_img"].shape
+    R = b["ref_imgs"].shape[1]
+    keep = [np.ascontiguousarray(x["key_img"]) for x in base] + [np.ascontiguousarray(x["ref_imgs"]) for x in base]
+    kp = (C.c_void_p * P)(*[keep[k % 2].ctypes.data for k in range(P)])
+    rp = (C.c_void_p * (P * R))(*[keep[2 + k % 2].ctypes.data + r * H * W * 8 for k in range(P) for r in range(R)])
+    od, ov = np.empty((P, H, W)), np.empty((P, H, W))
+    of = np.full((P, H, W), 99, dtype=np.int64)
+    am = np.empty((P, H, W), dtype=np.int32)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p)
+
+    def call(age):
+        return _lib.update_depth_frames_host(kp, p(b["key_cam"]), p(b["T_wk"]), rp, p(b["ref_cams"]), p(b["T_wr"]),
+                                             p(age), p(b["prior_depth"]), p(b["prior_variance"]), p(b["params"]),
+                                             P, R, H, W, p(od), p(ov), p(of), p(am), None, 0)
+
+    _lib.check(call(b["age"]))
+    orc = _oracle(b)
+    assert_parity([od, ov, of, am], orc)
+    for bad_age in (2, 255, 300, 2 ** 40 + 1):     # 2**40 + 1 would read as 1 if the wire just truncated
+        age = b["age"].copy()
+        age[69, 17, 23] = bad_age
+        assert call(age) == _lib.ERR_AGE
+    _lib.check(call(b["age"]))                     # and the entry point works again afterwards
+    assert_parity([od, ov, of, am], orc)
+
+
 def _fuse_reference(b, orc):
     """prior (+) oracle measurement where SUCCESS, composed from IEEE numpy ops in the order of
     propagation.rs:27-34 / fusion.rs:3-11."""

@@ -60,7 +60,8 @@ def test_keyframe_loop_matches_oracle_frame_by_frame():
         g_img1 = cu(img1)
         g_fd, g_fv, g_f = device.update_depth_frames(g_img1, g_cam, cu(T_w1), g_refs,
                                                      cu(np.tile(cam, (R, 1))), cu(np.stack(poses)),
-                                                     g_age1, g_d1, g_v1, params, fuse=True)
+                                                     g_age1, g_d1, g_v1, params, fuse=True,
+                                                     device_tables=bool(i % 2))   # both forms of the pointer tables
         g_reg = device.regularize(g_fd, g_fv, g_f)
         # ---- compare
         assert np.array_equal(g_age1.cpu().numpy(), o_age1), f"age differs at frame {i}"
