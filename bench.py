@@ -752,6 +752,8 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
+        # the host-pointer entry point converts ages and flags on a pool of host threads: share the cores between ranks
+        os.environ.setdefault("TDK_HOST_THREADS", str(max(2, min(8, (os.cpu_count() or 8) // max(1, world)))))
         run_b200(args, rank, world, local_rank)
 
 
