@@ -214,6 +214,12 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
                                  double *out_depth, double *out_variance, int64_t *out_flag,
                                  int32_t *dbg_argmin, uint64_t *out_hist, int fuse_on_success);
 
+/* Self-test of the host half of tdk_update_depth_frames_host's byte wire (needs no GPU): the ages go
+ * through the worker pool's narrowing (saturating at 255) and come back widened, the flags (-128 ..
+ * 127) come back through its widening.  No counterpart in the reference. */
+int tdk_selftest_host_wire(const uint64_t *age, const int64_t *flag, int64_t n, uint64_t *age_back,
+                           int64_t *flag_back);
+
 /* Replaces rust_bindings.semi_dense.estimate_debug_ (src/py/semi_dense.rs:126-155): one pixel,
  * host pointers, returns the prior on failure.  u_key is (x, y).  out = {depth, variance},
  * *out_flag the flag, dbg (optional, 1 value) = argmin+2 of the search, or -1. */

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include <atomic>
 #include <chrono>
@@ -80,7 +81,15 @@ class HostPool {
 public:
     static HostPool &get()
     {
-        static HostPool *pool = new HostPool;
+        // one pool per process: a child of fork() has none of the parent's threads, so it makes its own
+        static std::mutex guard;
+        static HostPool *pool = nullptr;
+        static pid_t owner = 0;
+        std::lock_guard<std::mutex> lk(guard);
+        if (!pool || owner != getpid()) {
+            pool = new HostPool;
+            owner = getpid();
+        }
         return *pool;
     }
     void submit(std::function<void()> fn)
@@ -659,6 +668,35 @@ int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double
 #endif
     if (rc == TDK_OK) rc = status_report(st_host, nchunks);
     return rc;
+}
+
+// Host half of the byte wire on its own (no device needed): ages -> bytes -> back, flags -> bytes ->
+// back through the worker pool, in quarter-frame tasks as tdk_update_depth_frames_host issues them.
+int tdk_selftest_host_wire(const uint64_t *age, const int64_t *flag, int64_t n, uint64_t *age_back, int64_t *flag_back)
+{
+    if (!age || !flag || !age_back || !flag_back || n < 0) {
+        tdk_set_error("tdk_selftest_host_wire: bad argument");
+        return TDK_ERR_INVALID;
+    }
+    std::vector<unsigned char> a8((size_t)n);
+    std::vector<signed char> f8((size_t)n);
+    for (int64_t i = 0; i < n; i++) f8[i] = (signed char)flag[i];   // what narrow_flag_kernel stores
+    ChunkSync sync(2);
+    const int pieces = (int)(((size_t)n + HOST_PIECE - 1) / HOST_PIECE);
+    if (pieces == 0) return TDK_OK;
+    sync.begin(sync.narrow_left, 0, pieces);
+    sync.begin(sync.widen_left, 1, pieces);
+    for (size_t o = 0; o < (size_t)n; o += HOST_PIECE) {
+        const size_t len = (size_t)n - o < HOST_PIECE ? (size_t)n - o : HOST_PIECE;
+        unsigned char *a = a8.data();
+        const signed char *f = f8.data();
+        HostPool::get().submit([=, &sync] { narrow_age_host(age + o, a + o, len); sync.end(sync.narrow_left, 0); });
+        HostPool::get().submit([=, &sync] { widen_flag_host(f + o, flag_back + o, len); sync.end(sync.widen_left, 1); });
+    }
+    sync.wait(sync.narrow_left, 0);
+    sync.drain();
+    for (int64_t i = 0; i < n; i++) age_back[i] = a8[i];   // what widen_age_kernel stores
+    return TDK_OK;
 }
 
 int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double prior_variance,
