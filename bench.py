@@ -581,6 +581,11 @@ def run_b200(args, rank, world, local_rank):
         import companion_bench
         companions = companion_bench.run(frames=64, iters=10)
         torch.cuda.empty_cache()
+    # ---- the numpy drop-in, one call per frame (what a user of the reference's module writes)
+    dropin = None
+    if rank == 0 and world == 1 and not args.no_c4:
+        import dropin_bench
+        dropin = dropin_bench.run(refs=R, iters=20)
 
     # ---- C5: the sharded run with the gather inside the clock (all ranks take part)
     c5 = None
@@ -691,7 +696,7 @@ def run_b200(args, rank, world, local_rank):
             "c4_720p_ms_per_pair": c4_ms, "c4_pairs_per_launch": args.c4_pairs if c4_ms is not None else None,
             "c3_vo_loop_ms_per_frame": c3_ms, "c3_vo_loop_f64_frames_ms_per_frame": c3_f64_ms,
             "c3_frames": "30 x 640x480, 8-bit gray frames from the host, one tdk_mapper_track call per frame",
-            "companions": companions, "c5": c5,
+            "companions": companions, "dropin_ms_per_call": dropin, "c5": c5,
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -753,7 +758,7 @@ def main():
         run_reference(args, rank, world)
     else:
         # the host-pointer entry point converts ages and flags on a pool of host threads: share the cores between ranks
-        os.environ.setdefault("TDK_HOST_THREADS", str(max(2, min(8, (os.cpu_count() or 8) // max(1, world)))))
+        os.environ.setdefault("TDK_HOST_THREADS", str(max(2, min(6, (os.cpu_count() or 8) // max(1, world)))))
         run_b200(args, rank, world, local_rank)
 
 

@@ -50,6 +50,8 @@ update_depth_static_dev = _sig("tdk_update_depth_static_dev", C.c_int, P, P, P, 
                                P, I64, I64, I64, I64, P, P, P, P, P, C.c_int, C.c_int, P)
 STATIC_MAX_PAIRS = 64
 update_depth_status = _sig("tdk_update_depth_status", C.c_int, P, P)
+update_depth_maps_host = _sig("tdk_update_depth_maps_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64, I64,
+                              I64, P, P, P, P, P, C.c_int)
 selftest_host_wire = _sig("tdk_selftest_host_wire", C.c_int, P, P, I64, P, P)
 update_depth_host = _sig("tdk_update_depth_host", C.c_int, P, P, P, P, P, P, P, P, P, P, I64, I64,
                          I64, I64, P, P, P, P, P, C.c_int)
@@ -114,7 +116,7 @@ EXPORTS = [
     "tdk_last_error", "tdk_version", "tdk_set_kernel_plan", "tdk_update_depth_workspace_bytes",
     "tdk_update_depth_workspace_bytes_min",
     "tdk_update_depth_dev", "tdk_update_depth_frames_dev", "tdk_update_depth_tables_dev", "tdk_update_depth_status",
-    "tdk_update_depth_static_dev", "tdk_selftest_host_wire",
+    "tdk_update_depth_static_dev", "tdk_selftest_host_wire", "tdk_update_depth_maps_host",
     "tdk_update_depth_host", "tdk_estimate_debug_host", "tdk_fusion_dev", "tdk_regularize_dev",
     "tdk_increment_age_workspace_bytes", "tdk_increment_age_dev", "tdk_propagate_workspace_bytes",
     "tdk_propagate_dev", "tdk_warp_vecs_dev", "tdk_interpolate_dev", "tdk_project_vecs_dev",

@@ -68,6 +68,8 @@ struct Arena {
     std::vector<cudaEvent_t> events; // grow-only pool (tdk_update_depth_frames_host: three per chunk)
     unsigned char *wire_host = nullptr;   // pinned, grow-only: 8-bit age maps going up, 8-bit flag maps coming back
     size_t wire_bytes = 0;
+    unsigned char *stage_host = nullptr;  // pinned ring of the pageable-memory path (struct Stage): 2 x 32 slots of 512 KB
+    cudaEvent_t stage_ev[64] = {};
 };
 
 // ---- host workers of the narrow-wire path (tdk_update_depth_frames_host)
@@ -76,7 +78,8 @@ struct Arena {
 // ahead of the uploads and widen the flag maps into the caller's array behind the read-backs; two
 // small kernels do the opposite on the device.  The pool is created on first use and never
 // destroyed (its threads sleep on a condition variable; a heap object, so no static destructor
-// runs under them).  TDK_HOST_THREADS sets its size (default: min(8, hardware threads)).
+// runs under them).  TDK_HOST_THREADS sets its size (default: min(6, hardware threads): 3-6 serve one
+// numpy call best, 8 contend on the page faults of fresh output arrays; the batched call is indifferent from 4 up).
 class HostPool {
 public:
     static HostPool &get()
@@ -97,6 +100,7 @@ public:
         {
             std::lock_guard<std::mutex> lk(m_);
             q_.push_back(std::move(fn));
+            queued_.fetch_add(1, std::memory_order_release);
         }
         cv_.notify_one();
     }
@@ -108,7 +112,7 @@ private:
         if (const char *e = getenv("TDK_HOST_THREADS")) n = atoi(e);
         if (n <= 0) {
             n = (int)std::thread::hardware_concurrency();
-            if (n > 8) n = 8;
+            if (n > 6) n = 6;
         }
         if (n < 1) n = 1;
         for (int i = 0; i < n; i++) std::thread([this] { loop(); }).detach();
@@ -117,15 +121,23 @@ private:
     {
         for (;;) {
             std::function<void()> fn;
+            // stay hot for a moment after the last task: pieces of one call arrive microseconds apart
+            for (int spins = 0; queued_.load(std::memory_order_acquire) == 0 && spins < 5000; spins++) {
+#if defined(__x86_64__) || defined(__i386__)
+                __builtin_ia32_pause();
+#endif
+            }
             {
                 std::unique_lock<std::mutex> lk(m_);
                 cv_.wait(lk, [this] { return !q_.empty(); });
                 fn = std::move(q_.front());
                 q_.pop_front();
+                queued_.fetch_sub(1, std::memory_order_relaxed);
             }
             fn();
         }
     }
+    std::atomic<int> queued_{0};
     std::mutex m_;
     std::condition_variable cv_;
     std::deque<std::function<void()>> q_;
@@ -773,12 +785,94 @@ int tdk_estimate_debug_host(const int64_t *u_key, double prior_depth, double pri
 // ---- host-pointer forms of the companions: copy in, run the *_dev entry point, copy out, one
 // stream of the per-device arena, returns when the results are in host memory.
 namespace {
+// Copies between the caller's host arrays and the device.  Pinned memory goes straight to
+// cudaMemcpyAsync.  Pageable memory (a numpy array) would be staged by the driver on the calling
+// thread at 10-15 GB/s; instead the worker pool copies it through a ring of pinned 512 KB slots,
+// piece by piece, and the DMA of a piece starts as soon as it is in its slot (uploads) or the
+// workers pick a piece up as soon as its DMA is through (read-backs).
+constexpr size_t STAGE_PIECE = (size_t)512 << 10;
+constexpr int STAGE_SLOTS = 32;                  // per direction: 16 MB in flight each way
+constexpr size_t STAGE_MIN = (size_t)128 << 10;  // smaller copies are not worth a hand-over
+
+// A short wait is cheaper spun than slept: a futex wake-up costs tens of microseconds, a 512 KB memcpy less.
+inline void spin_pause(int &spins)
+{
+    if (++spins < 4096) {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#endif
+    } else {
+        std::this_thread::yield();
+    }
+}
+
+struct Tickets {   // completion of tasks handed to the pool
+    std::deque<std::atomic<int>> done;   // a deque never moves its elements: workers hold pointers into it
+    std::atomic<int64_t> pending{0};
+    std::atomic<int> *issue()
+    {
+        done.emplace_back(0);
+        pending.fetch_add(1, std::memory_order_relaxed);
+        return &done.back();
+    }
+    void finish(std::atomic<int> *t)
+    {
+        t->store(1, std::memory_order_release);
+        pending.fetch_sub(1, std::memory_order_release);
+    }
+    void wait(std::atomic<int> *t)
+    {
+        int spins = 0;
+        while (!t->load(std::memory_order_acquire)) spin_pause(spins);
+    }
+    void drain()
+    {
+        int spins = 0;
+        while (pending.load(std::memory_order_acquire) != 0) spin_pause(spins);
+    }
+};
+
+bool is_pageable(const void *p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return at.type == cudaMemoryTypeUnregistered;
+}
+
+// fills `len` bytes of a pinned slot with what belongs at byte offset `off` of the device buffer
+typedef std::function<void(unsigned char *slot, size_t off, size_t len)> FillFn;
+// takes `len` bytes of a pinned slot that came from byte offset `off` of the device buffer
+typedef std::function<void(const unsigned char *slot, size_t off, size_t len)> DrainFn;
+
 struct Stage {
     Arena *ar = nullptr;
     cudaStream_t st = nullptr;
     size_t off = 0;
+    Tickets tickets;
+    int up_next = 0, down_next = 0;
+    bool up_used[STAGE_SLOTS] = {}, down_used[STAGE_SLOTS] = {};
+    struct Pending { int slot; size_t off, len; DrainFn fn; };
+    std::deque<Pending> pend;   // read-backs whose DMA is queued, oldest first
     void *take(size_t bytes) { void *p = (char *)ar->base + off; off += up256(bytes); return p; }
+    ~Stage() { tickets.drain(); }   // no worker may outlive the frame its task points into
+    unsigned char *up_slot(int i) { return ar->stage_host + (size_t)i * STAGE_PIECE; }
+    unsigned char *down_slot(int i) { return ar->stage_host + (size_t)(STAGE_SLOTS + i) * STAGE_PIECE; }
+    cudaEvent_t up_ev(int i) { return ar->stage_ev[i]; }
+    cudaEvent_t down_ev(int i) { return ar->stage_ev[STAGE_SLOTS + i]; }
 };
+
+int stage_ring_get(Arena *ar)
+{
+    if (!ar->stage_host) {
+        TDK_CUDA(cudaMallocHost((void **)&ar->stage_host, 2 * STAGE_SLOTS * STAGE_PIECE));
+        for (int i = 0; i < 2 * STAGE_SLOTS; i++) TDK_CUDA(cudaEventCreateWithFlags(&ar->stage_ev[i], cudaEventDisableTiming));
+    }
+    return TDK_OK;
+}
+
 int stage_open(size_t bytes, Stage *s)
 {
     int rc = arena_get(bytes, &s->ar);
@@ -787,16 +881,185 @@ int stage_open(size_t bytes, Stage *s)
     s->off = 0;
     return TDK_OK;
 }
+
+// upload of `bytes` device bytes produced piecewise by `fill` on the worker pool
+int up_pieces(Stage &s, void *dst, size_t bytes, const FillFn &fill)
+{
+    int rc = stage_ring_get(s.ar);
+    if (rc != TDK_OK) return rc;
+    for (size_t o = 0; o < bytes;) {
+        struct Piece { int slot; size_t off, len; std::atomic<int> *ticket; } win[STAGE_SLOTS];
+        int w = 0;
+        for (; w < STAGE_SLOTS && o < bytes; w++) {
+            Piece &q = win[w];
+            q.slot = s.up_next++ % STAGE_SLOTS;
+            q.off = o;
+            q.len = bytes - o < STAGE_PIECE ? bytes - o : STAGE_PIECE;
+            o += q.len;
+            if (s.up_used[q.slot]) TDK_CUDA(cudaEventSynchronize(s.up_ev(q.slot)));   // its last DMA has read it
+            q.ticket = s.tickets.issue();
+            unsigned char *slot = s.up_slot(q.slot);
+            const size_t off = q.off, len = q.len;
+            std::atomic<int> *t = q.ticket;
+            Tickets *tk = &s.tickets;
+            HostPool::get().submit([=] { fill(slot, off, len); tk->finish(t); });
+        }
+        for (int i = 0; i < w; i++) {
+            s.tickets.wait(win[i].ticket);
+            TDK_CUDA(cudaMemcpyAsync((char *)dst + win[i].off, s.up_slot(win[i].slot), win[i].len, cudaMemcpyHostToDevice, s.st));
+            TDK_CUDA(cudaEventRecord(s.up_ev(win[i].slot), s.st));
+            s.up_used[win[i].slot] = true;
+        }
+    }
+    return TDK_OK;
+}
+
+// hands the oldest queued read-back to the workers; wait = also until they are through with it
+int retire_one(Stage &s, bool wait)
+{
+    Stage::Pending q = s.pend.front();
+    s.pend.pop_front();
+    TDK_CUDA(cudaEventSynchronize(s.down_ev(q.slot)));
+    std::atomic<int> *t = s.tickets.issue();
+    const unsigned char *slot = s.down_slot(q.slot);
+    Tickets *tk = &s.tickets;
+    HostPool::get().submit([=] { q.fn(slot, q.off, q.len); tk->finish(t); });
+    if (wait) s.tickets.wait(t);
+    return TDK_OK;
+}
+
+// read-back of `bytes` device bytes consumed piecewise by `drain` on the worker pool (after stage_finish)
+int down_pieces(Stage &s, const void *src, size_t bytes, const DrainFn &drain)
+{
+    int rc = stage_ring_get(s.ar);
+    if (rc != TDK_OK) return rc;
+    for (size_t o = 0; o < bytes;) {
+        const int slot = s.down_next++ % STAGE_SLOTS;
+        const size_t len = bytes - o < STAGE_PIECE ? bytes - o : STAGE_PIECE;
+        if (s.down_used[slot]) {   // the ring came round: everything up to its last user has to leave first
+            while (!s.pend.empty()) {
+                const bool last = s.pend.front().slot == slot;
+                if ((rc = retire_one(s, true)) != TDK_OK) return rc;
+                if (last) break;
+            }
+        }
+        TDK_CUDA(cudaMemcpyAsync(s.down_slot(slot), (const char *)src + o, len, cudaMemcpyDeviceToHost, s.st));
+        TDK_CUDA(cudaEventRecord(s.down_ev(slot), s.st));
+        s.down_used[slot] = true;
+        s.pend.push_back({slot, o, len, drain});
+        o += len;
+    }
+    return TDK_OK;
+}
+
 int up(Stage &s, void *dst, const void *src, size_t bytes)
 {
+    if (bytes >= STAGE_MIN && is_pageable(src)) {
+        const unsigned char *from = (const unsigned char *)src;
+        return up_pieces(s, dst, bytes, [from](unsigned char *slot, size_t off, size_t len) { memcpy(slot, from + off, len); });
+    }
     return tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s.st), "H2D");
 }
+
 int down(Stage &s, void *dst, const void *src, size_t bytes)
 {
+    if (bytes >= STAGE_MIN && is_pageable(dst)) {
+        unsigned char *to = (unsigned char *)dst;
+        return down_pieces(s, src, bytes, [to](const unsigned char *slot, size_t off, size_t len) { memcpy(to + off, slot, len); });
+    }
     return tdk_check_cuda(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s.st), "D2H");
+}
+
+// everything queued on the stage is done and every read-back is in the caller's memory
+int stage_finish(Stage &s)
+{
+    int rc = TDK_OK;
+    while (!s.pend.empty() && rc == TDK_OK) rc = retire_one(s, false);
+    s.tickets.drain();
+    const int rc2 = tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return rc != TDK_OK ? rc : rc2;
 }
 #define TDK_RC(call) do { rc = (call); if (rc != TDK_OK) return rc; } while (0)
 }  // namespace
+
+// One call of the numpy drop-in's update_depth (rust_bindings.semi_dense.update_depth,
+// src/py/semi_dense.rs:157-187) for a caller that keeps its frames on the device: the images are
+// DEVICE pointers (host tables, as tdk_update_depth_frames_dev), cameras, poses and the maps are HOST
+// arrays, pageable or pinned.  Ages and flags cross the link as bytes when R < 255.
+int tdk_update_depth_maps_host(const double *const *key_img_ptrs, const double *key_cams, const double *T_wk,
+                               const double *const *ref_img_ptrs, const double *ref_cams, const double *T_wr,
+                               const uint64_t *age, const double *prior_depth, const double *prior_variance,
+                               const double *params, int64_t P, int64_t R, int64_t H, int64_t W, double *out_depth,
+                               double *out_variance, int64_t *out_flag, int32_t *dbg_argmin, uint64_t *out_hist,
+                               int fuse_on_success)
+{
+    TdkRange range("tdk_update_depth_maps_host");
+    if (!key_img_ptrs || !ref_img_ptrs || !key_cams || !T_wk || !ref_cams || !T_wr || !age || !prior_depth ||
+        !prior_variance || !params || !out_depth || !out_variance || !out_flag) {
+        tdk_set_error("tdk_update_depth_maps_host: null pointer argument");
+        return TDK_ERR_INVALID;
+    }
+    if (P <= 0 || R <= 0 || H <= 0 || W <= 0) {
+        tdk_set_error("tdk_update_depth_maps_host: bad sizes");
+        return TDK_ERR_INVALID;
+    }
+    int dev = 0, rc = current_device(&dev);
+    if (rc != TDK_OK) return rc;
+    std::lock_guard<std::mutex> lock(g_mutex[dev]);
+    const size_t n = (size_t)P * H * W, wsb = tdk_update_depth_workspace_bytes(P, R, H, W);
+    const bool narrow = R < 255;
+    Stage s;
+    TDK_RC(stage_open(up256(n * 8) * 6 + up256(n) * 2 + up256(n * 4) + up256(P * 80) + up256(P * 32) + up256(P * 128) +
+                          up256(P * R * 32) + up256(P * R * 128) + 512 + up256(wsb), &s));
+    if ((rc = status_host_get(s.ar, 1)) != TDK_OK) return rc;
+    uint64_t *d_age = (uint64_t *)s.take(n * 8);
+    double *d_pd = (double *)s.take(n * 8), *d_pv = (double *)s.take(n * 8);
+    double *d_od = (double *)s.take(n * 8), *d_ov = (double *)s.take(n * 8);
+    int64_t *d_of = (int64_t *)s.take(n * 8);
+    unsigned char *d_age8 = (unsigned char *)s.take(n);
+    signed char *d_of8 = (signed char *)s.take(n);
+    int32_t *d_dbg = dbg_argmin ? (int32_t *)s.take(n * 4) : nullptr;
+    uint64_t *d_hist = out_hist ? (uint64_t *)s.take(P * 80) : nullptr;
+    double *d_kc = (double *)s.take(P * 32), *d_Twk = (double *)s.take(P * 128);
+    double *d_rc = (double *)s.take(P * R * 32), *d_Twr = (double *)s.take(P * R * 128);
+    int *d_status = (int *)s.take(256);
+    void *ws = s.take(wsb);
+    const unsigned blocks = (unsigned)((n + 2047) / 2048);
+    TDK_RC(up(s, d_kc, key_cams, P * 32));
+    TDK_RC(up(s, d_Twk, T_wk, P * 128));
+    TDK_RC(up(s, d_rc, ref_cams, P * R * 32));
+    TDK_RC(up(s, d_Twr, T_wr, P * R * 128));
+    if (narrow) {
+        TDK_RC(up_pieces(s, d_age8, n, [age](unsigned char *slot, size_t off, size_t len) { narrow_age_host(age + off, slot, len); }));
+        widen_age_kernel<<<blocks, 256, 0, s.st>>>(d_age8, d_age, n);
+        TDK_RC(tdk_check_cuda(cudaGetLastError(), "widen_age_kernel"));
+    } else {
+        TDK_RC(up(s, d_age, age, n * 8));
+    }
+    TDK_RC(up(s, d_pd, prior_depth, n * 8));
+    TDK_RC(up(s, d_pv, prior_variance, n * 8));
+    if (d_hist) TDK_RC(tdk_check_cuda(cudaMemsetAsync(d_hist, 0, P * 80, s.st), "memset hist"));
+    TDK_RC(tdk_update_depth_frames_dev(key_img_ptrs, d_kc, d_Twk, ref_img_ptrs, d_rc, d_Twr, d_age, d_pd, d_pv, params, P, R,
+                                       H, W, d_od, d_ov, d_of, d_dbg, d_hist, fuse_on_success, ws, wsb, s.st));
+    if (narrow) {
+        narrow_flag_kernel<<<blocks, 256, 0, s.st>>>(d_of, d_of8, n, (const int *)ws, d_status);
+        TDK_RC(tdk_check_cuda(cudaGetLastError(), "narrow_flag_kernel"));
+    }
+    TDK_RC(down(s, out_depth, d_od, n * 8));
+    TDK_RC(down(s, out_variance, d_ov, n * 8));
+    if (narrow) {
+        TDK_RC(down_pieces(s, d_of8, n, [out_flag](const unsigned char *slot, size_t off, size_t len) {
+            widen_flag_host((const signed char *)slot, out_flag + off, len);
+        }));
+    } else {
+        TDK_RC(down(s, out_flag, d_of, n * 8));
+    }
+    if (dbg_argmin) TDK_RC(down(s, dbg_argmin, d_dbg, n * 4));
+    if (out_hist) TDK_RC(down(s, out_hist, d_hist, P * 80));
+    TDK_RC(tdk_check_cuda(cudaMemcpyAsync(s.ar->status_host, ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, s.st), "D2H status"));
+    TDK_RC(stage_finish(s));
+    return status_report(reinterpret_cast<const int(*)[TDK_ST_WORDS]>(s.ar->status_host), 1);
+}
 
 int tdk_increment_age_host(const uint64_t *age0, const double *cam0, const double *cam1, const double *T10,
                            const double *depth0, int64_t P, int64_t H, int64_t W, uint64_t *age1)
@@ -823,7 +1086,7 @@ int tdk_increment_age_host(const uint64_t *age0, const double *cam0, const doubl
     TDK_RC(up(s, d_T, T10, P * 128));
     TDK_RC(tdk_increment_age_dev(d_age0, d_c0, d_c1, d_T, d_depth, P, H, W, d_age1, ws, wsb, s.st));
     TDK_RC(down(s, age1, d_age1, n * 8));
-    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return stage_finish(s);
 }
 
 int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1, const double *depth0,
@@ -854,7 +1117,7 @@ int tdk_propagate_host(const double *T10, const double *cam0, const double *cam1
                              uncertaintity_bias, d_d1, d_v1, ws, wsb, s.st));
     TDK_RC(down(s, depth1, d_d1, n * 8));
     TDK_RC(down(s, variance1, d_v1, n * 8));
-    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return stage_finish(s);
 }
 
 int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, const double *var2,
@@ -882,7 +1145,7 @@ int tdk_fusion_host(const double *mu1, const double *mu2, const double *var1, co
     TDK_RC(tdk_fusion_dev(d_m1, d_m2, d_v1, d_v2, d_f, n, depth_domain, d_mu, d_var, s.st));
     TDK_RC(down(s, mu, d_mu, b));
     TDK_RC(down(s, var, d_var, b));
-    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return stage_finish(s);
 }
 
 int tdk_regularize_host(const double *depth, const double *variance, const int64_t *flag, int64_t P, int64_t H,
@@ -906,7 +1169,7 @@ int tdk_regularize_host(const double *depth, const double *variance, const int64
     TDK_RC(up(s, d_f, flag, b));
     TDK_RC(tdk_regularize_dev(d_d, d_v, d_f, P, H, W, d_o, s.st));
     TDK_RC(down(s, out_depth, d_o, b));
-    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return stage_finish(s);
 }
 
 }  // extern "C"
@@ -938,7 +1201,7 @@ int run_staged(const char *who, const In (&in)[NI], const Out (&out)[NO], Body b
     TDK_RC(body(din, dout, s.st));
     for (int i = 0; i < NO; i++)
         if (out[i].bytes) TDK_RC(down(s, out[i].host, dout[i], out[i].bytes));
-    return tdk_check_cuda(cudaStreamSynchronize(s.st), "cudaStreamSynchronize");
+    return stage_finish(s);
 }
 }  // namespace
 

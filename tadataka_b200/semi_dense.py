@@ -29,6 +29,10 @@ def _need(a, name, dtype, ndim):
     return np.ascontiguousarray(a)
 
 
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
 def _cuda(a):
     """numpy -> CUDA tensor on the current device (pageable H2D copy)."""
     device._require_cuda()
@@ -69,6 +73,7 @@ class Frame:
         dev = torch.cuda.current_device()
         if self._dev is None or self._dev.device.index != dev:
             self._dev = _cuda(self._image)
+            torch.cuda.current_stream().synchronize()   # the C-ABI call reads it from the library's own stream
         return self._dev
 
 
@@ -117,13 +122,20 @@ def update_depth(keyframe, refframes, age_map, prior_depth, prior_variance, para
             raise ValueError("Age exceeds the refframe size")
         return (prior_depth.copy(), prior_variance.copy(),
                 np.full(shape, int(ResultFlag.NOT_PROCESSED), dtype=np.int64))
-    ref_cams = _cuda(np.stack([f._cam for f in refframes]))
-    T_wr = _cuda(np.stack([f._transform for f in refframes]))
-    d, v, fl = device.update_depth_frames(
-        keyframe.device_image(), _cuda(keyframe._cam), _cuda(keyframe._transform),
-        [f.device_image() for f in refframes], ref_cams, T_wr, _cuda(age_map), _cuda(prior_depth),
-        _cuda(prior_variance), params)
-    return d.cpu().numpy(), v.cpu().numpy(), fl.cpu().numpy()
+    # frames stay on the device (uploaded once per Frame); cameras, poses and the maps go through
+    # ONE host-pointer C-ABI call, which moves the numpy maps through the library's pinned ring
+    R = len(refframes)
+    H, W = shape
+    ref_cams = np.ascontiguousarray(np.stack([f._cam for f in refframes]))
+    T_wr = np.ascontiguousarray(np.stack([f._transform for f in refframes]))
+    key_ptr = (C.c_void_p * 1)(keyframe.device_image().data_ptr())
+    ref_ptr = (C.c_void_p * R)(*[f.device_image().data_ptr() for f in refframes])
+    d, v = np.empty(shape), np.empty(shape)
+    fl = np.empty(shape, dtype=np.int64)
+    _lib.check(_lib.update_depth_maps_host(key_ptr, _p(keyframe._cam), _p(keyframe._transform), ref_ptr, _p(ref_cams),
+                                           _p(T_wr), _p(age_map), _p(prior_depth), _p(prior_variance),
+                                           _p(params.as_array()), 1, R, H, W, _p(d), _p(v), _p(fl), None, None, 0))
+    return d, v, fl
 
 
 def estimate_debug_(u_key, prior_depth, prior_variance, keyframe, refframe, params):
@@ -150,10 +162,6 @@ def estimate_debug_(u_key, prior_depth, prior_variance, keyframe, refframe, para
                                   p(params.as_array()), H, W, p(out), p(flag), None)
     _lib.check(rc)
     return float(out[0]), float(out[1]), int(flag[0])
-
-
-def _p(a):
-    return a.ctypes.data_as(C.c_void_p)
 
 
 def propagate(transform10, camera_params0, camera_params1, depth_map0, variance_map0,

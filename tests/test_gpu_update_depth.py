@@ -348,6 +348,49 @@ def test_frames_host_byte_wire_ring_and_age_errors():
     assert_parity([od, ov, of, am], orc)
 
 
+def test_maps_host_entry_point_pageable_and_pinned():
+    """tdk_update_depth_maps_host: frames on the device, maps in host memory.  8 VGA keyframes make
+    every map 19.7 MB, so the 16 MB pinned ring of the pageable path comes round; the same call
+    with pinned maps takes the direct path.  Both equal the oracle, argmin and histogram included."""
+    import ctypes as C
+    from tadataka_b200 import _lib
+    items = [scene.make_keyframe(880 + i, R=2) for i in range(2)] * 4
+    rng = np.random.default_rng(88)
+    items = [dict(it, prior_variance=np.ascontiguousarray(10.0 ** rng.uniform(-3.0, 0.0, size=it["prior_variance"].shape)))
+             for it in items]
+    b = scene.stack_keyframes(items)
+    P, H, W = b["key_img"].shape
+    R = b["ref_imgs"].shape[1]
+    g_key, g_ref = torch.from_numpy(b["key_img"]).cuda(), torch.from_numpy(b["ref_imgs"]).cuda()
+    torch.cuda.synchronize()
+    kp = (C.c_void_p * P)(*[g_key[k].data_ptr() for k in range(P)])
+    rp = (C.c_void_p * (P * R))(*[g_ref[k, r].data_ptr() for k in range(P) for r in range(R)])
+    orc = _oracle(b)
+
+    def p(a):
+        return C.c_void_p(a.data_ptr()) if isinstance(a, torch.Tensor) else a.ctypes.data_as(C.c_void_p)
+
+    for pinned in (False, True):
+        def host(a):
+            return torch.from_numpy(a).pin_memory() if pinned else a
+        age, pd, pv = host(b["age"].view(np.int64)), host(b["prior_depth"]), host(b["prior_variance"])
+        od, ov = host(np.empty((P, H, W))), host(np.empty((P, H, W)))
+        of = host(np.full((P, H, W), 99, dtype=np.int64))
+        am = host(np.empty((P, H, W), dtype=np.int32))
+        hist = np.zeros((P, 10), dtype=np.uint64)
+        rc = _lib.update_depth_maps_host(kp, p(b["key_cam"]), p(b["T_wk"]), rp, p(b["ref_cams"]), p(b["T_wr"]), p(age),
+                                         p(pd), p(pv), p(b["params"]), P, R, H, W, p(od), p(ov), p(of), p(am), p(hist), 0)
+        _lib.check(rc)
+        got = [x.numpy() if isinstance(x, torch.Tensor) else x for x in (od, ov, of, am)]
+        assert_parity(got, orc)
+        assert [int(x) for x in hist.sum(0)] == [int((orc[2] == -k).sum()) for k in range(10)]
+    bad = b["age"].copy()
+    bad[3, 5, 7] = 2 ** 33
+    assert _lib.update_depth_maps_host(kp, p(b["key_cam"]), p(b["T_wk"]), rp, p(b["ref_cams"]), p(b["T_wr"]), p(bad),
+                                       p(b["prior_depth"]), p(b["prior_variance"]), p(b["params"]), P, R, H, W,
+                                       p(od), p(ov), p(of), None, None, 0) == _lib.ERR_AGE
+
+
 def _fuse_reference(b, orc):
     """prior (+) oracle measurement where SUCCESS, composed from IEEE numpy ops in the order of
     propagation.rs:27-34 / fusion.rs:3-11."""
