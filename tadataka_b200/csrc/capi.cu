@@ -883,7 +883,7 @@ int stage_open(size_t bytes, Stage *s)
 }
 
 // upload of `bytes` device bytes produced piecewise by `fill` on the worker pool
-int up_pieces(Stage &s, void *dst, size_t bytes, const FillFn &fill)
+int up_pieces(Stage &s, void *dst, size_t bytes, const FillFn &fill, size_t piece = STAGE_PIECE)
 {
     int rc = stage_ring_get(s.ar);
     if (rc != TDK_OK) return rc;
@@ -894,7 +894,7 @@ int up_pieces(Stage &s, void *dst, size_t bytes, const FillFn &fill)
             Piece &q = win[w];
             q.slot = s.up_next++ % STAGE_SLOTS;
             q.off = o;
-            q.len = bytes - o < STAGE_PIECE ? bytes - o : STAGE_PIECE;
+            q.len = bytes - o < piece ? bytes - o : piece;
             o += q.len;
             if (s.up_used[q.slot]) TDK_CUDA(cudaEventSynchronize(s.up_ev(q.slot)));   // its last DMA has read it
             q.ticket = s.tickets.issue();
@@ -929,13 +929,13 @@ int retire_one(Stage &s, bool wait)
 }
 
 // read-back of `bytes` device bytes consumed piecewise by `drain` on the worker pool (after stage_finish)
-int down_pieces(Stage &s, const void *src, size_t bytes, const DrainFn &drain)
+int down_pieces(Stage &s, const void *src, size_t bytes, const DrainFn &drain, size_t piece = STAGE_PIECE)
 {
     int rc = stage_ring_get(s.ar);
     if (rc != TDK_OK) return rc;
     for (size_t o = 0; o < bytes;) {
         const int slot = s.down_next++ % STAGE_SLOTS;
-        const size_t len = bytes - o < STAGE_PIECE ? bytes - o : STAGE_PIECE;
+        const size_t len = bytes - o < piece ? bytes - o : piece;
         if (s.down_used[slot]) {   // the ring came round: everything up to its last user has to leave first
             while (!s.pend.empty()) {
                 const bool last = s.pend.front().slot == slot;
@@ -1025,12 +1025,15 @@ int tdk_update_depth_maps_host(const double *const *key_img_ptrs, const double *
     int *d_status = (int *)s.take(256);
     void *ws = s.take(wsb);
     const unsigned blocks = (unsigned)((n + 2047) / 2048);
+#ifdef TDK_HOST_TIMING
+    const double t0 = host_now();
+#endif
     TDK_RC(up(s, d_kc, key_cams, P * 32));
     TDK_RC(up(s, d_Twk, T_wk, P * 128));
     TDK_RC(up(s, d_rc, ref_cams, P * R * 32));
     TDK_RC(up(s, d_Twr, T_wr, P * R * 128));
     if (narrow) {
-        TDK_RC(up_pieces(s, d_age8, n, [age](unsigned char *slot, size_t off, size_t len) { narrow_age_host(age + off, slot, len); }));
+        TDK_RC(up_pieces(s, d_age8, n, [age](unsigned char *slot, size_t off, size_t len) { narrow_age_host(age + off, slot, len); }, STAGE_PIECE / 8));   // a piece = 512 KB of the CALLER's array
         widen_age_kernel<<<blocks, 256, 0, s.st>>>(d_age8, d_age, n);
         TDK_RC(tdk_check_cuda(cudaGetLastError(), "widen_age_kernel"));
     } else {
@@ -1039,25 +1042,38 @@ int tdk_update_depth_maps_host(const double *const *key_img_ptrs, const double *
     TDK_RC(up(s, d_pd, prior_depth, n * 8));
     TDK_RC(up(s, d_pv, prior_variance, n * 8));
     if (d_hist) TDK_RC(tdk_check_cuda(cudaMemsetAsync(d_hist, 0, P * 80, s.st), "memset hist"));
+#ifdef TDK_HOST_TIMING
+    const double t1 = host_now();
+#endif
     TDK_RC(tdk_update_depth_frames_dev(key_img_ptrs, d_kc, d_Twk, ref_img_ptrs, d_rc, d_Twr, d_age, d_pd, d_pv, params, P, R,
                                        H, W, d_od, d_ov, d_of, d_dbg, d_hist, fuse_on_success, ws, wsb, s.st));
     if (narrow) {
         narrow_flag_kernel<<<blocks, 256, 0, s.st>>>(d_of, d_of8, n, (const int *)ws, d_status);
         TDK_RC(tdk_check_cuda(cudaGetLastError(), "narrow_flag_kernel"));
     }
+#ifdef TDK_HOST_TIMING
+    const double t2 = host_now();
+#endif
     TDK_RC(down(s, out_depth, d_od, n * 8));
     TDK_RC(down(s, out_variance, d_ov, n * 8));
     if (narrow) {
         TDK_RC(down_pieces(s, d_of8, n, [out_flag](const unsigned char *slot, size_t off, size_t len) {
             widen_flag_host((const signed char *)slot, out_flag + off, len);
-        }));
+        }, STAGE_PIECE / 8));
     } else {
         TDK_RC(down(s, out_flag, d_of, n * 8));
     }
     if (dbg_argmin) TDK_RC(down(s, dbg_argmin, d_dbg, n * 4));
     if (out_hist) TDK_RC(down(s, out_hist, d_hist, P * 80));
     TDK_RC(tdk_check_cuda(cudaMemcpyAsync(s.ar->status_host, ws, sizeof(int) * TDK_ST_WORDS, cudaMemcpyDeviceToHost, s.st), "D2H status"));
+#ifdef TDK_HOST_TIMING
+    const double t3 = host_now();
+#endif
     TDK_RC(stage_finish(s));
+#ifdef TDK_HOST_TIMING
+    fprintf(stderr, "maps_host: uploads %.0f us, launches %.0f us, read-backs queued %.0f us, finish %.0f us\n",
+            1e6 * (t1 - t0), 1e6 * (t2 - t1), 1e6 * (t3 - t2), 1e6 * (host_now() - t3));
+#endif
     return status_report(reinterpret_cast<const int(*)[TDK_ST_WORDS]>(s.ar->status_host), 1);
 }
 
