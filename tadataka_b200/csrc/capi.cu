@@ -1,6 +1,8 @@
 // Host-side plumbing of the C-ABI: error text, version, and the host-pointer entry points
-// (copy in -> launch -> copy out), which stage through a grow-only per-device arena and
-// pipeline chunks of keyframes over three streams so that H2D, kernels and D2H overlap.
+// (copy in -> launch -> copy out), which stage through a grow-only per-device arena.  The batched
+// update_depth forms pipeline chunks of keyframes over several streams so that H2D, kernels and D2H
+// overlap; a small pool of host threads narrows / widens the byte-wide maps and moves pageable
+// caller memory through pinned rings.
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -439,8 +441,9 @@ int tdk_update_depth_host(const double *key_imgs, const double *key_cams, const 
 // update_depth from host memory with frames passed by POINTER: an image that several keyframes
 // name -- the reference frames of the reference's own loop, examples/semi_dense_vo.py:196-203, where
 // every keyframe is matched against the frames before it -- crosses PCIe once.  Chunks of keyframes
-// rotate over three streams; the images a chunk needs that are not on the device yet go up on the
-// first stream just before it, so image upload, kernels and the copy back of earlier chunks overlap.
+// rotate over FRAMES_SLOTS streams; the images a chunk needs that are not on the device yet go up on
+// a stream of their own just before it, so image upload, kernels and the copy back of earlier chunks
+// overlap.  Cameras, poses and pointer tables go up once; ages and flags travel as bytes (R < 255).
 int tdk_update_depth_frames_host(const double *const *key_img_ptrs, const double *key_cams, const double *T_wk,
                                  const double *const *ref_img_ptrs, const double *ref_cams, const double *T_wr,
                                  const uint64_t *age, const double *prior_depth, const double *prior_variance,
