@@ -58,7 +58,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--keyframes", type=int, default=64, help="keyframes per GPU per step")
     ap.add_argument("--distinct", type=int, default=8, help="distinct rendered scenes per GPU")
-    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 10)")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = min(steps, 30)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c4", action="store_true", help="skip the secondary 1280x720 and keyframe-loop measurements")
     ap.add_argument("--c4-pairs", type=int, default=64, help="1280x720 pairs per launch (BASELINE.json configs[3])")
@@ -594,7 +594,7 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.empty_cache()
 
     # ---- e2e: host-pointer C-ABI call, pinned host buffers, copies inside the timed region
-    e2e_steps = args.e2e_steps or min(args.steps, 10)
+    e2e_steps = args.e2e_steps or min(args.steps, 30)
     h_out = (torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
              torch.empty((B, H, W), dtype=torch.float64).pin_memory(),
              torch.empty((B, H, W), dtype=torch.int64).pin_memory())
