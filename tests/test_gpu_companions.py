@@ -305,3 +305,51 @@ def test_estimate_debug_outside_the_image_returns_the_reference_flag():
                                       it["ref_cams"][0], it["T_wr"][0], ora.make_params(*pr))
             got = estimate_debug_(np.array(u, dtype=np.int64), d, v, key, ref, params)
             assert got == want and got[0] == d and got[1] == v and got[2] in (-2, -7, -1, -8), (u, d, v, got, want)
+
+
+def test_drop_in_calls_from_several_threads_at_once():
+    """Four Python threads call the numpy drop-in at the same time (ctypes releases the GIL): calls
+    on one device are serialised inside the library, the worker pool and the pinned rings are
+    shared -- every thread gets the oracle's maps for ITS keyframe."""
+    import threading
+    from rust_bindings.camera import CameraParameters
+    from rust_bindings.semi_dense import Frame, Params, increment_age, propagate, update_depth
+    from tadataka_b200 import scene
+    items = [scene.make_keyframe(640 + i, R=3, H=240, W=320, cam=scene.CAM_VGA / 2) for i in range(4)]
+    want, errors, got = [], [], [None] * 4
+    for it in items:
+        b = scene.stack_keyframes([it])
+        want.append(ora.update_depth_batch(b["key_img"], b["key_cam"], b["T_wk"], b["ref_imgs"], b["ref_cams"],
+                                           b["T_wr"], b["age"], b["prior_depth"], b["prior_variance"],
+                                           ora.make_params(*b["params"]))[:3])
+
+    def work(i):
+        try:
+            it = items[i]
+            cam = CameraParameters((it["key_cam"][0], it["key_cam"][1]), (it["key_cam"][2], it["key_cam"][3]))
+            key = Frame(cam, it["key_img"], it["T_wk"])
+            refs = [Frame(cam, it["ref_imgs"][r], it["T_wr"][r]) for r in range(3)]
+            params = Params(*[float(x) for x in it["params"]])
+            T10 = np.linalg.inv(it["T_wk"]) @ it["T_wr"][-1]
+            for _ in range(5):
+                d, v, f = update_depth(key, refs, it["age"], it["prior_depth"], it["prior_variance"], params)
+                a1 = increment_age(it["age"], cam, cam, T10, it["prior_depth"])
+                d1, v1 = propagate(T10, cam, cam, it["prior_depth"], it["prior_variance"], 200.0, 100.0, 1e-6)
+            got[i] = (d, v, f, a1, d1, v1)
+        except Exception as e:   # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not errors, errors
+    for i, it in enumerate(items):
+        d, v, f, a1, d1, v1 = got[i]
+        assert np.array_equal(f, want[i][2][0]) and np.array_equal(d, want[i][0][0]) and np.array_equal(v, want[i][1][0])
+        cam = it["key_cam"]
+        T10 = np.linalg.inv(it["T_wk"]) @ it["T_wr"][-1]
+        assert np.array_equal(a1, ora.increment_age(it["age"], cam, cam, T10, it["prior_depth"]))
+        od1, ov1 = ora.propagate(T10, cam, cam, it["prior_depth"], it["prior_variance"], 200.0, 100.0, 1e-6)
+        assert np.array_equal(d1, od1) and np.array_equal(v1, ov1)
