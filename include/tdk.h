@@ -433,7 +433,8 @@ int tdk_selftest_shared_division_dev(int64_t n, uint64_t seed, uint64_t *mismatc
  * One Gauss-Newton iteration of _PoseChangeEstimator.__call__ (:76-110) = one
  * tdk_dvo_normal_equations_dev (calc_pose_update, :46-73, with calc_jacobian of
  * tadataka/vo/dvo/jacobian.py:8-24) + one tdk_dvo_photometric_error_dev (tadataka/metric.py:13-39);
- * the 6x6 solve, the SE(3) exponential and the loop stay on the host (tadataka_b200/dvo.py).
+ * the 6x6 solve, the SE(3) exponential and the loop run on the host (tadataka_b200/dvo.py) or, for
+ * weight modes 0-2, on the device (tdk_dvo_iterate_dev).
  * Images, depth map, gradients, weights: device [H,W] f64.  cam0, cam1 (4 doubles each) and T10
  * (16 doubles, frame 1 <- frame 0) are HOST pointers, passed to the kernels by value.
  *
@@ -467,6 +468,20 @@ int tdk_dvo_student_t_dev(const double *I0, const double *D0, const double *I1, 
 int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const double *I1,
                                   const double *cam0, const double *cam1, const double *T10,
                                   int64_t H, int64_t W, double *out, void *stream);
+/* The whole Gauss-Newton loop of _PoseChangeEstimator.__call__ (tadataka/vo/dvo/__init__.py:76-110) at
+ * one resolution without a host round trip per iteration: max_iter times {normal equations, 6x6
+ * Cholesky solve, candidate = exp(xi) * T10 (pose.py:44-53, se3.py:16-31), photometric error of the
+ * candidate, accept unless the error rose (:100-108)}; kernels of iterations after the stop return
+ * at once.  weight_mode 0, 1 or 2 (3 and 4 need a scale per iteration).  cam0, cam1, T10 (4x4 start
+ * pose): host pointers.  state: 128 device doubles; when the stream has run: [0..15] the final T10
+ * (row-major), [66] status (0 ok; 1 no usable pixel -- the reference's "Camera pose change is too
+ * large"; 2 normal equations not positive definite -- solve on the host), [68] accepted steps,
+ * [69] the last accepted error. */
+int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, const double *GX1,
+                        const double *GY1, const double *weights, int weight_mode,
+                        double weight_param, const double *cam0, const double *cam1,
+                        const double *T10, int64_t H, int64_t W, int max_iter, double *state,
+                        void *stream);
 size_t tdk_dvo_tukey_workspace_bytes(int64_t H, int64_t W);
 int tdk_dvo_tukey_scale_dev(const double *I0, const double *D0, const double *I1, double c_mad,
                             const double *cam0, const double *cam1, const double *T10, int64_t H,

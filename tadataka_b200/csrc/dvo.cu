@@ -46,17 +46,26 @@ __global__ void __launch_bounds__(TPB) image_gradient_kernel(const double *__res
 }
 
 // warp of pixel (x, y): K1 * pi(T10 * pi^-1(K0^-1 u0, d))  (warp.py:78-88 / dvo __init__.py:93-96)
-__device__ __forceinline__ void warp_pixel(const DvoConst &c, int x, int y, double d, double &u, double &v,
-                                           double &px, double &py, double &pz)
+__device__ __forceinline__ void warp_pixel(const DvoConst &c, const double (&T)[12], int x, int y, double d,
+                                           double &u, double &v, double &px, double &py, double &pz)
 {
     const double x0 = ((double)x - c.o0x) / c.f0x, y0 = ((double)y - c.o0y) / c.f0y;
     const double p0 = x0 * d, p1 = y0 * d, p2 = 1. * d;
-    px = c.T[0] * p0 + c.T[1] * p1 + c.T[2] * p2 + c.T[3];
-    py = c.T[4] * p0 + c.T[5] * p1 + c.T[6] * p2 + c.T[7];
-    pz = c.T[8] * p0 + c.T[9] * p1 + c.T[10] * p2 + c.T[11];
+    px = T[0] * p0 + T[1] * p1 + T[2] * p2 + T[3];
+    py = T[4] * p0 + T[5] * p1 + T[6] * p2 + T[7];
+    pz = T[8] * p0 + T[9] * p1 + T[10] * p2 + T[11];
     const double z = pz + TDK_EPS;
     u = (px / z) * c.f1x + c.o1x;
     v = (py / z) * c.f1y + c.o1y;
+}
+
+// the pose a kernel works with: the launch's own (by value) or, in the device-resident loop, the one
+// in device memory.  Read into an array of its own: overwriting part of a local copy of the by-value
+// struct lost element 0 (nvcc 12.9 kept reading T[0] from the parameter).
+__device__ __forceinline__ void load_pose(const DvoConst &c, const double *__restrict__ T_dev, double (&T)[12])
+{
+#pragma unroll
+    for (int k = 0; k < 12; k++) T[k] = T_dev ? T_dev[k] : c.T[k];
 }
 
 template <int N>
@@ -106,8 +115,13 @@ __device__ __forceinline__ double row_weight(int mode, double param, double nu, 
 __global__ void __launch_bounds__(TPB) dvo_normal_equations_kernel(
     const double *__restrict__ I0, const double *__restrict__ D0, const double *__restrict__ I1,
     const double *__restrict__ GX1, const double *__restrict__ GY1, const double *__restrict__ wmap, int mode,
-    double wparam, double nu, const DvoConst c, int H, int W, double *__restrict__ out)
+    double wparam, double nu, const DvoConst c0, int H, int W, double *__restrict__ out,
+    const double *__restrict__ T_dev = nullptr, const double *__restrict__ done = nullptr)
 {
+    if (done && *done != 0.) return;   // device-resident loop (tdk_dvo_iterate_dev): the iteration has stopped
+    const DvoConst &c = c0;
+    double T[12];
+    load_pose(c0, T_dev, T);
     __shared__ double s_acc[NACC];
     double acc[NACC];
 #pragma unroll
@@ -116,7 +130,7 @@ __global__ void __launch_bounds__(TPB) dvo_normal_equations_kernel(
     for (int i = blockIdx.x * TPB + threadIdx.x; i < hw; i += gridDim.x * TPB) {
         const int y = i / W, x = i - y * W;
         double u, v, px, py, pz;
-        warp_pixel(c, x, y, D0[i], u, v, px, py, pz);
+        warp_pixel(c, T, x, y, D0[i], u, v, px, py, pz);
         if (!(tdk::in_range(u, v, (double)W - 1., (double)H - 1.) && pz > 0.)) continue;
         const double gx = tdk::bilinear(GX1, W, H, u, v), gy = tdk::bilinear(GY1, W, H, u, v);
         const double r = I0[i] - I1[i];   // dvo __init__.py:90: residuals = (I0 - I1).flatten()
@@ -160,7 +174,7 @@ __global__ void __launch_bounds__(TPB) dvo_student_t_kernel(const double *__rest
     for (int i = blockIdx.x * TPB + threadIdx.x; i < hw; i += gridDim.x * TPB) {
         const int y = i / W, x = i - y * W;
         double u, v, px, py, pz;
-        warp_pixel(c, x, y, D0[i], u, v, px, py, pz);
+        warp_pixel(c, c.T, x, y, D0[i], u, v, px, py, pz);
         if (!(tdk::in_range(u, v, (double)W - 1., (double)H - 1.) && pz > 0.)) continue;
         const double r = I0[i] - I1[i];
         const double s = r * r;
@@ -175,16 +189,22 @@ __global__ void __launch_bounds__(TPB) dvo_student_t_kernel(const double *__rest
 __global__ void __launch_bounds__(TPB) dvo_photometric_error_kernel(const double *__restrict__ I0,
                                                                     const double *__restrict__ D0,
                                                                     const double *__restrict__ I1,
-                                                                    const DvoConst c, int H, int W,
-                                                                    double *__restrict__ out)
+                                                                    const DvoConst c0, int H, int W,
+                                                                    double *__restrict__ out,
+                                                                    const double *__restrict__ T_dev = nullptr,
+                                                                    const double *__restrict__ done = nullptr)
 {
+    if (done && *done != 0.) return;
+    const DvoConst &c = c0;
+    double T[12];
+    load_pose(c0, T_dev, T);
     __shared__ double s_acc[2];
     double acc[2] = {0., 0.};
     const int hw = H * W;
     for (int i = blockIdx.x * TPB + threadIdx.x; i < hw; i += gridDim.x * TPB) {
         const int y = i / W, x = i - y * W;
         double u, v, px, py, pz;
-        warp_pixel(c, x, y, D0[i], u, v, px, py, pz);
+        warp_pixel(c, T, x, y, D0[i], u, v, px, py, pz);
         if (!tdk::in_range(u, v, (double)W - 1., (double)H - 1.)) continue;
         const double d = I0[i] - tdk::bilinear(I1, W, H, u, v);
         acc[0] += d * d;
@@ -209,7 +229,7 @@ __global__ void __launch_bounds__(TPB) residual_compact_kernel(const double *__r
         if (i < hw) {
             const int y = i / W, x = i - y * W;
             double u, v, px, py, pz;
-            warp_pixel(c, x, y, D0[i], u, v, px, py, pz);
+            warp_pixel(c, c.T, x, y, D0[i], u, v, px, py, pz);
             ok = tdk::in_range(u, v, (double)W - 1., (double)H - 1.) && pz > 0.;
             r = I0[i] - I1[i];
         }
@@ -298,6 +318,135 @@ int check_image(const char *who, int64_t H, int64_t W, bool ptrs_ok)
         return TDK_ERR_INVALID;
     }
     return TDK_OK;
+}
+
+
+// ---- the Gauss-Newton loop of _PoseChangeEstimator.__call__ (dvo __init__.py:76-110) without a host
+// round trip per iteration.  State, in device doubles:
+enum { ST_T = 0, ST_CAND = 16, ST_NE = 32, ST_ERR = 64, ST_STATUS = 66, ST_DONE = 67, ST_ITERS = 68, ST_PREV = 69, ST_LAST_S = 70, ST_LAST_N = 71,
+       ST_WORDS = 128 };
+
+struct Pose16 { double m[16]; };
+
+__global__ void dvo_loop_init_kernel(double *__restrict__ st, const Pose16 T)
+{
+    const int i = threadIdx.x;
+    if (i < ST_WORDS) st[i] = i < 16 ? T.m[i] : 0.;
+}
+
+// after the first error evaluation: prev_error = mean over the usable pixels (nan when there is none, as np.mean)
+__global__ void dvo_loop_first_error_kernel(double *__restrict__ st)
+{
+    st[ST_PREV] = st[ST_ERR + 1] > 0. ? st[ST_ERR] / st[ST_ERR + 1] : nan("");
+    st[ST_ERR] = 0.;
+    st[ST_ERR + 1] = 0.;
+}
+
+// xi = A^-1 b by Cholesky of the diagonally scaled A (A = J^T W J is symmetric, positive definite unless the scene is degenerate:
+// then status 2 and the host takes over with its minimum-norm solve), candidate = exp(xi) * T10
+// (pose.py:44-53, se3.py:16-31; the closed form of tadataka_b200/dvo.py exp_se3)
+__global__ void dvo_loop_solve_kernel(double *__restrict__ st)
+{
+    if (st[ST_DONE] != 0.) return;
+    const double *ne = st + ST_NE;
+    if (ne[27] == 0.) {   // no usable pixel: "Camera pose change is too large."
+        st[ST_STATUS] = 1.;
+        st[ST_DONE] = 1.;
+        return;
+    }
+    // Jacobi scaling first (translation and rotation columns differ by orders of magnitude): solve
+    // (S A S) z = S b with S = diag(A)^-1/2, xi = S z
+    double L[6][6], xi[6], y[6], sc[6];
+    int k = 0;
+    for (int a = 0; a < 6; a++)
+        for (int b = a; b < 6; b++) L[b][a] = ne[k++];   // lower triangle
+    bool ok = true;
+    for (int a = 0; a < 6; a++) {
+        if (!(L[a][a] > 0.) || !(L[a][a] < 1e300)) ok = false;
+        sc[a] = ok ? 1. / sqrt(L[a][a]) : 0.;
+    }
+    for (int a = 0; a < 6 && ok; a++)
+        for (int b = 0; b <= a; b++) L[a][b] = a == b ? 1. : L[a][b] * sc[a] * sc[b];
+    for (int j = 0; j < 6 && ok; j++) {
+        double d = L[j][j];
+        for (int m = 0; m < j; m++) d -= L[j][m] * L[j][m];
+        if (!(d > 1e-14)) { ok = false; break; }   // the scaled matrix has a unit diagonal
+        const double r = sqrt(d);
+        L[j][j] = r;
+        for (int i = j + 1; i < 6; i++) {
+            double v = L[i][j];
+            for (int m = 0; m < j; m++) v -= L[i][m] * L[j][m];
+            L[i][j] = v / r;
+        }
+    }
+    if (!ok) {
+        st[ST_STATUS] = 2.;
+        st[ST_DONE] = 1.;
+        return;
+    }
+    for (int i = 0; i < 6; i++) {
+        double v = ne[21 + i] * sc[i];
+        for (int m = 0; m < i; m++) v -= L[i][m] * y[m];
+        y[i] = v / L[i][i];
+    }
+    for (int i = 5; i >= 0; i--) {
+        double v = y[i];
+        for (int m = i + 1; m < 6; m++) v -= L[m][i] * xi[m];
+        xi[i] = v / L[i][i];
+    }
+    for (int i = 0; i < 6; i++) xi[i] *= sc[i];
+    // exp_se3: R = I + a W + b W^2, V = I + b W + c W^2 on the un-normalised skew matrix W = [w]x
+    const double wx = xi[3], wy = xi[4], wz = xi[5];
+    const double t2 = wx * wx + wy * wy + wz * wz;
+    double a, b, c;
+    if (t2 < 1e-6) {
+        a = 1. - t2 / 6. * (1. - t2 / 20.);
+        b = 0.5 - t2 / 24. * (1. - t2 / 30.);
+        c = 1. / 6. - t2 / 120. * (1. - t2 / 42.);
+    } else {
+        const double t = sqrt(t2), sn = sin(t), cs = cos(t);
+        a = sn / t;
+        b = (1. - cs) / t2;
+        c = (t - sn) / (t2 * t);
+    }
+    const double Wm[3][3] = {{0., -wz, wy}, {wz, 0., -wx}, {-wy, wx, 0.}};
+    double W2[3][3], E[4][4];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) W2[i][j] = Wm[i][0] * Wm[0][j] + Wm[i][1] * Wm[1][j] + Wm[i][2] * Wm[2][j];
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) E[i][j] = (i == j ? 1. : 0.) + a * Wm[i][j] + b * W2[i][j];
+        const double Wv = Wm[i][0] * xi[0] + Wm[i][1] * xi[1] + Wm[i][2] * xi[2];
+        const double W2v = W2[i][0] * xi[0] + W2[i][1] * xi[1] + W2[i][2] * xi[2];
+        E[i][3] = xi[i] + b * Wv + c * W2v;
+    }
+    E[3][0] = E[3][1] = E[3][2] = 0.;
+    E[3][3] = 1.;
+    const double *T = st + ST_T;
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++)
+            st[ST_CAND + i * 4 + j] = E[i][0] * T[j] + E[i][1] * T[4 + j] + E[i][2] * T[8 + j] + E[i][3] * T[12 + j];
+}
+
+// the accept / stop rule (dvo __init__.py:100-108): stop when the error rises, else take the candidate
+__global__ void dvo_loop_accept_kernel(double *__restrict__ st)
+{
+    const int i = threadIdx.x;
+    const bool done = st[ST_DONE] != 0.;
+    const double curr = st[ST_ERR + 1] > 0. ? st[ST_ERR] / st[ST_ERR + 1] : nan("");
+    const bool stop = curr > st[ST_PREV];   // false for nan, as in the reference
+    __syncthreads();
+    if (!done && !stop && i < 16) st[ST_T + i] = st[ST_CAND + i];
+    if (i >= 32 && i < 32 + NACC) st[ST_NE + (i - 32)] = 0.;   // accumulators of the next iteration
+    if (i == 0) {
+        if (!done) {
+            st[ST_LAST_S] = st[ST_ERR];
+            st[ST_LAST_N] = st[ST_ERR + 1];
+            if (stop) st[ST_DONE] = 1.;
+            else { st[ST_PREV] = curr; st[ST_ITERS] += 1.; }
+        }
+        st[ST_ERR] = 0.;
+        st[ST_ERR + 1] = 0.;
+    }
 }
 
 unsigned reduce_grid(int64_t hw)
@@ -393,6 +542,38 @@ int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const doub
     TDK_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), st));
     dvo_photometric_error_kernel<<<reduce_grid(H * W), TPB, 0, st>>>(I0, D0, I1, make_const(cam0, cam1, T10), (int)H,
                                                                     (int)W, out);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, const double *GX1, const double *GY1,
+                        const double *weights, int weight_mode, double weight_param, const double *cam0,
+                        const double *cam1, const double *T10, int64_t H, int64_t W, int max_iter, double *state,
+                        void *stream)
+{
+    int rc = check_image("tdk_dvo_iterate_dev", H, W, I0 && D0 && I1 && GX1 && GY1 && cam0 && cam1 && T10 && state);
+    if (rc != TDK_OK) return rc;
+    if (!(weight_mode == W_NONE || weight_mode == W_HUBER || (weight_mode == W_ARRAY && weights)) || max_iter < 0) {
+        tdk_set_error("tdk_dvo_iterate_dev: weight mode %d needs a scale per iteration (student-t, tukey): use the "
+                      "per-iteration entry points", weight_mode);
+        return TDK_ERR_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = reduce_grid(H * W);
+    Pose16 T;
+    for (int i = 0; i < 16; i++) T.m[i] = T10[i];
+    const DvoConst c = make_const(cam0, cam1, T10);
+    dvo_loop_init_kernel<<<1, ST_WORDS, 0, st>>>(state, T);
+    dvo_photometric_error_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, c, (int)H, (int)W, state + ST_ERR, state + ST_T, state + ST_DONE);
+    dvo_loop_first_error_kernel<<<1, 1, 0, st>>>(state);
+    for (int it = 0; it < max_iter; it++) {
+        dvo_normal_equations_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, GX1, GY1, weights, weight_mode, weight_param, 0., c,
+                                                          (int)H, (int)W, state + ST_NE, state + ST_T, state + ST_DONE);
+        dvo_loop_solve_kernel<<<1, 1, 0, st>>>(state);
+        dvo_photometric_error_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, c, (int)H, (int)W, state + ST_ERR, state + ST_CAND,
+                                                           state + ST_DONE);
+        dvo_loop_accept_kernel<<<1, 64, 0, st>>>(state);
+    }
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

@@ -5,9 +5,10 @@ variance maps `update_depth` produces).
 
 Per Gauss-Newton iteration the two per-pixel passes -- building J^T W J / J^T W r
 (calc_pose_update, :46-73) and re-evaluating the photometric error (tadataka/metric.py:13-39) --
-run as CUDA reductions (csrc/dvo.cu behind include/tdk.h); 30 + 2 doubles come back per iteration
-and the 6x6 solve, the SE(3) exponential (tadataka/se3.py:16-31) and the accept/stop rule
-(:98-108) run on the host.  Poses are 4x4 matrices T10 (frame 1 <- frame 0) instead of the
+run as CUDA reductions (csrc/dvo.cu behind include/tdk.h).  For weights None / map / "huber" the
+whole loop -- 6x6 solve, SE(3) exponential (tadataka/se3.py:16-31), accept/stop rule (:98-108) --
+stays on the device (tdk_dvo_iterate_dev, one read-back per resolution); for "student-t" / "tukey",
+or when a trace is asked for, 30 + 2 doubles come back per iteration and those steps run on the host.  Poses are 4x4 matrices T10 (frame 1 <- frame 0) instead of the
 reference's `Pose` objects.
 
 Deviations from the reference:
@@ -15,7 +16,6 @@ Deviations from the reference:
     running lstsq on the [N,6] system (tadataka/math.py:34-50): same minimiser, different rounding;
   * the image pyramid (:139-148) uses `rescale` below (Gaussian pre-filter + bilinear), not
     skimage.transform.rescale, which is not available here;
-  * weights="tukey" (median based) is not provided on the device.
 """
 import ctypes as C
 import warnings
@@ -185,7 +185,37 @@ def estimate_pose_change(camera_params0, camera_params1, I0, D0, I1, T10=None, w
                     max_iter, trace)
 
 
+def _iterate_on_device(level, T10, weights, max_iter):
+    """The whole Gauss-Newton loop in one C-ABI call (tdk_dvo_iterate_dev): normal equations, 6x6
+    Cholesky solve, SE(3) exponential, error of the candidate and the accept / stop rule all run on
+    the device; one read-back at the end.  For weights None / a weight map / "huber" (student-t and
+    tukey need a scale per iteration that is found with host logic).  Returns T10, or None when the
+    normal equations were not positive definite (the host loop then decides with its lstsq)."""
+    mode, param, wmap = 0, 0.0, None
+    if isinstance(weights, str):
+        mode, param = 2, HUBER_K
+    elif weights is not None:
+        mode, wmap = 1, level.W0
+    T10 = np.ascontiguousarray(T10, dtype=np.float64)
+    state = torch.empty(128, dtype=_F64, device=level.I0.device)
+    _lib.check(_lib.dvo_iterate_dev(
+        device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1), device._ptr(level.GX1),
+        device._ptr(level.GY1), device._ptr(wmap), mode, float(param), _vp(level.cam0), _vp(level.cam1), _vp(T10),
+        level.H, level.W, int(max_iter), device._ptr(state), device._stream()))
+    st = state.cpu().numpy()
+    status = int(st[66])
+    if status == 2:
+        return None
+    if status == 1:
+        warnings.warn("Camera pose change is too large.", RuntimeWarning)
+    return st[:16].reshape(4, 4).copy()
+
+
 def _iterate(level, T10, weights, max_iter, trace=None):
+    if trace is None and (weights is None or not isinstance(weights, str) or weights == "huber"):
+        T = _iterate_on_device(level, T10, weights, max_iter)
+        if T is not None:
+            return T
     prev_error = level.photometric_error(T10)
     for _ in range(max_iter):
         ne = level.normal_equations(T10, weights)

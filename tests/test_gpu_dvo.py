@@ -132,3 +132,42 @@ def test_pyramid_estimator_and_error_cases():
     with pytest.warns(RuntimeWarning, match="too large"):
         out = dvo.estimate_pose_change(cam, cam, I0, D0, I1, far, None, max_iter=3)
     assert np.array_equal(out, far)
+
+
+@pytest.mark.parametrize("weights", [None, "huber", "map"])
+def test_device_resident_loop_equals_the_host_loop_and_the_oracle(weights):
+    """tdk_dvo_iterate_dev (solve, exponential and accept / stop rule on the device) against the
+    per-iteration host loop of the same kernels (trace given) and against the numpy oracle."""
+    from tadataka_b200 import dvo
+    # a motion large enough for ten or so accepted steps: every one of them reads the pose the
+    # previous one left in device memory (a pose element dropped there shows up as 1e-2 in the result)
+    cam, I0, D0, I1, _ = _pair(seed=9100, H=240, W=320, t=(6.0, -2.5, 3.5), rot=(0.012, -0.018, 0.009))
+    if weights == "map":
+        rng = np.random.default_rng(4)
+        weights = rng.uniform(0.2, 1.0, size=I0.shape)
+    trace = []
+    T_host = dvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), weights, max_iter=20, trace=trace)
+    T_dev = dvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), weights, max_iter=20)
+    oT = odvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), weights, max_iter=20)
+    assert np.max(np.abs(T_dev - T_host)) <= 1e-9
+    assert np.max(np.abs(T_dev - oT)) <= ATOL_POSE
+    # the loop's own bookkeeping: as many accepted steps as the host loop took before its error rose
+    level = dvo._Level(cam, cam, I0, D0, I1, weights if isinstance(weights, np.ndarray) else None)
+    import torch
+    from tadataka_b200 import _lib, device
+    state = torch.empty(128, dtype=torch.float64, device="cuda")
+    T0 = np.eye(4)
+    mode = 2 if isinstance(weights, str) else (1 if weights is not None else 0)
+    _lib.check(_lib.dvo_iterate_dev(device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1),
+                                    device._ptr(level.GX1), device._ptr(level.GY1), device._ptr(level.W0), mode,
+                                    dvo.HUBER_K if mode == 2 else 0.0, dvo._vp(level.cam0), dvo._vp(level.cam1),
+                                    dvo._vp(T0), level.H, level.W, 20, device._ptr(state), device._stream()))
+    st = state.cpu().numpy()
+    accepted_host = len(trace) - 1 if len(trace) < 20 or trace[-1][1] > trace[-2][1] else len(trace)
+    assert int(st[66]) == 0 and int(st[68]) == accepted_host and accepted_host >= 4
+    # zero iterations: the start pose comes back untouched
+    _lib.check(_lib.dvo_iterate_dev(device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1),
+                                    device._ptr(level.GX1), device._ptr(level.GY1), device._ptr(level.W0), mode,
+                                    dvo.HUBER_K if mode == 2 else 0.0, dvo._vp(level.cam0), dvo._vp(level.cam1),
+                                    dvo._vp(T_dev), level.H, level.W, 0, device._ptr(state), device._stream()))
+    assert np.array_equal(state.cpu().numpy()[:16].reshape(4, 4), T_dev)

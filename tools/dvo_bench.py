@@ -61,3 +61,23 @@ oT = odvo.estimate_pose_change(cam, cam, I0, D0, I1, np.eye(4), None, max_iter=2
 t_cpu = time.perf_counter() - t0
 print(f"full single-level estimate ({len(trace)} iterations): GPU {t_gpu * 1e3:.1f} ms, numpy oracle {t_cpu * 1e3:.1f} ms, "
       f"max |dT| {np.max(np.abs(T - oT)):.2e}")
+
+# the loop alone, images already on the device: per-iteration host round trips against tdk_dvo_iterate_dev
+for name, T_w, in (("small motion", T_w1), ("larger motion", scene.pose(scene.rotation(0.012, -0.018, 0.009), (6.0, -2.5, 3.5)))):
+    J1, _ = world.render(T_w, cam, H, W)
+    lv = dvo._Level(cam, cam, I0, D0, J1)
+    for w in (None, "huber"):
+        tr = []
+        dvo._iterate(lv, np.eye(4), w, 20, tr)
+        dvo._iterate(lv, np.eye(4), w, 20)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(10):
+            Th = dvo._iterate(lv, np.eye(4), w, 20, [])
+        t_host = (time.perf_counter() - t0) / 10
+        t0 = time.perf_counter()
+        for _ in range(10):
+            Td = dvo._iterate(lv, np.eye(4), w, 20)
+        t_dev = (time.perf_counter() - t0) / 10
+        print(f"{name}, weights {w}: {len(tr)} iterations; host loop {t_host * 1e3:.2f} ms, device loop {t_dev * 1e3:.2f} ms, "
+              f"max |dT| {np.max(np.abs(Th - Td)):.1e}")
