@@ -476,12 +476,15 @@ int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const doub
  * pose): host pointers.  state: 128 device doubles; when the stream has run: [0..15] the final T10
  * (row-major), [66] status (0 ok; 1 no usable pixel -- the reference's "Camera pose change is too
  * large"; 2 normal equations not positive definite -- solve on the host), [68] accepted steps,
- * [69] the last accepted error. */
+ * [67] 1 when the loop has stopped by its own rule, [69] the last accepted error.  Every queued
+ * iteration costs four launches even when the loop stopped earlier, so a caller that expects few
+ * iterations queues a few, looks at [67], and calls again with resume = 1 (same inputs, same state:
+ * max_iter MORE iterations, nothing re-initialised; T10 is ignored). */
 int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, const double *GX1,
                         const double *GY1, const double *weights, int weight_mode,
                         double weight_param, const double *cam0, const double *cam1,
-                        const double *T10, int64_t H, int64_t W, int max_iter, double *state,
-                        void *stream);
+                        const double *T10, int64_t H, int64_t W, int max_iter, int resume,
+                        double *state, void *stream);
 size_t tdk_dvo_tukey_workspace_bytes(int64_t H, int64_t W);
 int tdk_dvo_tukey_scale_dev(const double *I0, const double *D0, const double *I1, double c_mad,
                             const double *cam0, const double *cam1, const double *T10, int64_t H,

@@ -108,7 +108,8 @@ dvo_student_t_dev = _sig("tdk_dvo_student_t_dev", C.c_int, P, P, P, D, D, P, P, 
 dvo_photometric_error_dev = _sig("tdk_dvo_photometric_error_dev", C.c_int, P, P, P, P, P, P, I64, I64, P,
                                  P)
 
-dvo_iterate_dev = _sig("tdk_dvo_iterate_dev", C.c_int, P, P, P, P, P, P, C.c_int, D, P, P, P, I64, I64, C.c_int, P, P)
+dvo_iterate_dev = _sig("tdk_dvo_iterate_dev", C.c_int, P, P, P, P, P, P, C.c_int, D, P, P, P, I64, I64, C.c_int, C.c_int,
+                       P, P)
 dvo_tukey_workspace_bytes = _sig("tdk_dvo_tukey_workspace_bytes", SZ, I64, I64)
 dvo_tukey_scale_dev = _sig("tdk_dvo_tukey_scale_dev", C.c_int, P, P, P, D, P, P, P, I64, I64, P, P, SZ, P)
 

@@ -548,8 +548,8 @@ int tdk_dvo_photometric_error_dev(const double *I0, const double *D0, const doub
 
 int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, const double *GX1, const double *GY1,
                         const double *weights, int weight_mode, double weight_param, const double *cam0,
-                        const double *cam1, const double *T10, int64_t H, int64_t W, int max_iter, double *state,
-                        void *stream)
+                        const double *cam1, const double *T10, int64_t H, int64_t W, int max_iter, int resume,
+                        double *state, void *stream)
 {
     int rc = check_image("tdk_dvo_iterate_dev", H, W, I0 && D0 && I1 && GX1 && GY1 && cam0 && cam1 && T10 && state);
     if (rc != TDK_OK) return rc;
@@ -563,9 +563,11 @@ int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, co
     Pose16 T;
     for (int i = 0; i < 16; i++) T.m[i] = T10[i];
     const DvoConst c = make_const(cam0, cam1, T10);
-    dvo_loop_init_kernel<<<1, ST_WORDS, 0, st>>>(state, T);
-    dvo_photometric_error_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, c, (int)H, (int)W, state + ST_ERR, state + ST_T, state + ST_DONE);
-    dvo_loop_first_error_kernel<<<1, 1, 0, st>>>(state);
+    if (!resume) {   // resume: `state` holds an unfinished loop of the same inputs; max_iter more iterations
+        dvo_loop_init_kernel<<<1, ST_WORDS, 0, st>>>(state, T);
+        dvo_photometric_error_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, c, (int)H, (int)W, state + ST_ERR, state + ST_T, state + ST_DONE);
+        dvo_loop_first_error_kernel<<<1, 1, 0, st>>>(state);
+    }
     for (int it = 0; it < max_iter; it++) {
         dvo_normal_equations_kernel<<<grid, TPB, 0, st>>>(I0, D0, I1, GX1, GY1, weights, weight_mode, weight_param, 0., c,
                                                           (int)H, (int)W, state + ST_NE, state + ST_T, state + ST_DONE);

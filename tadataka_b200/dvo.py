@@ -198,11 +198,20 @@ def _iterate_on_device(level, T10, weights, max_iter):
         mode, wmap = 1, level.W0
     T10 = np.ascontiguousarray(T10, dtype=np.float64)
     state = torch.empty(128, dtype=_F64, device=level.I0.device)
-    _lib.check(_lib.dvo_iterate_dev(
-        device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1), device._ptr(level.GX1),
-        device._ptr(level.GY1), device._ptr(wmap), mode, float(param), _vp(level.cam0), _vp(level.cam1), _vp(T10),
-        level.H, level.W, int(max_iter), device._ptr(state), device._stream()))
-    st = state.cpu().numpy()
+    # iterations are queued in growing batches (4, 8, 16, ...): a queued iteration costs four launches even
+    # after the loop has stopped, a look at the state costs one small read-back
+    queued, batch, st = 0, 4, None
+    while True:
+        n = min(batch, max_iter - queued)
+        _lib.check(_lib.dvo_iterate_dev(
+            device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1), device._ptr(level.GX1),
+            device._ptr(level.GY1), device._ptr(wmap), mode, float(param), _vp(level.cam0), _vp(level.cam1), _vp(T10),
+            level.H, level.W, int(n), int(queued > 0), device._ptr(state), device._stream()))
+        queued += n
+        st = state.cpu().numpy()
+        if st[67] != 0. or queued >= max_iter:
+            break
+        batch *= 2
     status = int(st[66])
     if status == 2:
         return None

@@ -161,13 +161,15 @@ def test_device_resident_loop_equals_the_host_loop_and_the_oracle(weights):
     _lib.check(_lib.dvo_iterate_dev(device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1),
                                     device._ptr(level.GX1), device._ptr(level.GY1), device._ptr(level.W0), mode,
                                     dvo.HUBER_K if mode == 2 else 0.0, dvo._vp(level.cam0), dvo._vp(level.cam1),
-                                    dvo._vp(T0), level.H, level.W, 20, device._ptr(state), device._stream()))
+                                    dvo._vp(T0), level.H, level.W, 20, 0, device._ptr(state), device._stream()))
     st = state.cpu().numpy()
     accepted_host = len(trace) - 1 if len(trace) < 20 or trace[-1][1] > trace[-2][1] else len(trace)
     assert int(st[66]) == 0 and int(st[68]) == accepted_host and accepted_host >= 4
+    # queued all at once (here) or in batches with resume (estimate_pose_change): the same walk
+    assert np.max(np.abs(st[:16].reshape(4, 4) - T_dev)) <= 1e-9 and st[67] == 1.0
     # zero iterations: the start pose comes back untouched
     _lib.check(_lib.dvo_iterate_dev(device._ptr(level.I0), device._ptr(level.D0), device._ptr(level.I1),
                                     device._ptr(level.GX1), device._ptr(level.GY1), device._ptr(level.W0), mode,
                                     dvo.HUBER_K if mode == 2 else 0.0, dvo._vp(level.cam0), dvo._vp(level.cam1),
-                                    dvo._vp(T_dev), level.H, level.W, 0, device._ptr(state), device._stream()))
+                                    dvo._vp(T_dev), level.H, level.W, 0, 0, device._ptr(state), device._stream()))
     assert np.array_equal(state.cpu().numpy()[:16].reshape(4, 4), T_dev)
