@@ -485,6 +485,17 @@ int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, co
                         double weight_param, const double *cam0, const double *cam1,
                         const double *T10, int64_t H, int64_t W, int max_iter, int resume,
                         double *state, void *stream);
+/* The image pyramid of PoseChangeEstimator.__call__ (tadataka/vo/dvo/__init__.py:139-148:
+ * skimage.transform.rescale per level) on the device, in the form tadataka_b200/dvo.py `rescale`
+ * gives it (skimage is not available here; the pyramid is unpinned, see DESIGN):
+ * tdk_gaussian_blur_dev  = scipy.ndimage.gaussian_filter(mode="reflect"): two separable passes with
+ *   the 2*radius+1 normalised weights the HOST array `kernel` holds (radius <= 32); tmp, out: [H,W].
+ * tdk_resample_bilinear_dev = scipy.ndimage.map_coordinates(order=1, mode="reflect") on the grid
+ *   ((i + 0.5) / scale - 0.5, (j + 0.5) / scale - 0.5), i < h, j < w. */
+int tdk_gaussian_blur_dev(const double *image, int64_t H, int64_t W, const double *kernel, int radius,
+                          double *tmp, double *out, void *stream);
+int tdk_resample_bilinear_dev(const double *image, int64_t H, int64_t W, double scale, double *out,
+                              int64_t h, int64_t w, void *stream);
 size_t tdk_dvo_tukey_workspace_bytes(int64_t H, int64_t W);
 int tdk_dvo_tukey_scale_dev(const double *I0, const double *D0, const double *I1, double c_mad,
                             const double *cam0, const double *cam1, const double *T10, int64_t H,

@@ -110,6 +110,8 @@ dvo_photometric_error_dev = _sig("tdk_dvo_photometric_error_dev", C.c_int, P, P,
 
 dvo_iterate_dev = _sig("tdk_dvo_iterate_dev", C.c_int, P, P, P, P, P, P, C.c_int, D, P, P, P, I64, I64, C.c_int, C.c_int,
                        P, P)
+gaussian_blur_dev = _sig("tdk_gaussian_blur_dev", C.c_int, P, I64, I64, P, C.c_int, P, P, P)
+resample_bilinear_dev = _sig("tdk_resample_bilinear_dev", C.c_int, P, I64, I64, D, P, I64, I64, P)
 dvo_tukey_workspace_bytes = _sig("tdk_dvo_tukey_workspace_bytes", SZ, I64, I64)
 dvo_tukey_scale_dev = _sig("tdk_dvo_tukey_scale_dev", C.c_int, P, P, P, D, P, P, P, I64, I64, P, P, SZ, P)
 
@@ -125,7 +127,7 @@ EXPORTS = [
     "tdk_inv_project_vecs_dev", "tdk_transform_dev", "tdk_calc_depth0_dev",
     "tdk_selftest_shared_division_dev", "tdk_render_scene_dev", "tdk_age_usage_dev", "tdk_propagate_age_dev", "tdk_sqrt_threshold",
     "tdk_image_gradient_dev", "tdk_dvo_normal_equations_dev", "tdk_dvo_student_t_dev",
-    "tdk_dvo_photometric_error_dev", "tdk_dvo_iterate_dev",
+    "tdk_dvo_photometric_error_dev", "tdk_dvo_iterate_dev", "tdk_gaussian_blur_dev", "tdk_resample_bilinear_dev",
     "tdk_increment_age_host", "tdk_propagate_host", "tdk_fusion_host", "tdk_regularize_host",
     "tdk_mapper_arena_bytes", "tdk_mapper_create", "tdk_mapper_destroy", "tdk_mapper_reset", "tdk_mapper_track",
     "tdk_mapper_sync", "tdk_mapper_prune", "tdk_mapper_state",

@@ -449,6 +449,49 @@ __global__ void dvo_loop_accept_kernel(double *__restrict__ st)
     }
 }
 
+// ---- image pyramid of PoseChangeEstimator.__call__ (dvo __init__.py:139-148) on the device: the
+// Gaussian pre-filter and the bilinear resampling of tadataka_b200/dvo.py `rescale` (scipy's
+// gaussian_filter(mode="reflect", truncate=4) and map_coordinates(order=1, mode="reflect")).
+constexpr int GAUSS_MAX_RADIUS = 32;
+struct GaussKernel { int radius; double w[2 * GAUSS_MAX_RADIUS + 1]; };
+
+__device__ __forceinline__ int reflect_index(int j, int n)   // d c b a | a b c d | d c b a
+{
+    while (j < 0 || j >= n) j = j < 0 ? -j - 1 : 2 * n - 1 - j;
+    return j;
+}
+
+// one separable pass along axis 0 (rows: stride W) or axis 1
+__global__ void __launch_bounds__(TPB) gauss_blur_axis_kernel(const double *__restrict__ in, double *__restrict__ out,
+                                                              int H, int W, int axis, const GaussKernel g)
+{
+    const int x = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (x >= W || y >= H) return;
+    double acc = 0.;
+    for (int k = -g.radius; k <= g.radius; k++) {
+        const double v = axis == 0 ? in[(size_t)reflect_index(y + k, H) * W + x] : in[(size_t)y * W + reflect_index(x + k, W)];
+        acc += g.w[k + g.radius] * v;
+    }
+    out[(size_t)y * W + x] = acc;
+}
+
+// out[i, j] = image sampled bilinearly at ((i + 0.5) / scale - 0.5, (j + 0.5) / scale - 0.5)
+__global__ void __launch_bounds__(TPB) resample_bilinear_kernel(const double *__restrict__ in, int H, int W,
+                                                                double *__restrict__ out, int h, int w, double scale)
+{
+    const int j = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int i = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (j >= w || i >= h) return;
+    const double cy = ((double)i + 0.5) / scale - 0.5, cx = ((double)j + 0.5) / scale - 0.5;
+    const double fy = floor(cy), fx = floor(cx), ty = cy - fy, tx = cx - fx;
+    const int y0 = reflect_index((int)fy, H), y1 = reflect_index((int)fy + 1, H);
+    const int x0 = reflect_index((int)fx, W), x1 = reflect_index((int)fx + 1, W);
+    const double a = in[(size_t)y0 * W + x0], b = in[(size_t)y0 * W + x1];
+    const double c = in[(size_t)y1 * W + x0], d = in[(size_t)y1 * W + x1];
+    out[(size_t)i * w + j] = (1. - ty) * ((1. - tx) * a + tx * b) + ty * ((1. - tx) * c + tx * d);
+}
+
 unsigned reduce_grid(int64_t hw)
 {
     const int64_t blocks = (hw + TPB - 1) / TPB;
@@ -576,6 +619,41 @@ int tdk_dvo_iterate_dev(const double *I0, const double *D0, const double *I1, co
                                                            state + ST_DONE);
         dvo_loop_accept_kernel<<<1, 64, 0, st>>>(state);
     }
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_gaussian_blur_dev(const double *image, int64_t H, int64_t W, const double *kernel, int radius, double *tmp,
+                          double *out, void *stream)
+{
+    int rc = check_image("tdk_gaussian_blur_dev", H, W, image && kernel && tmp && out);
+    if (rc != TDK_OK) return rc;
+    if (radius < 0 || radius > GAUSS_MAX_RADIUS) {
+        tdk_set_error("tdk_gaussian_blur_dev: radius %d outside 0..%d", radius, GAUSS_MAX_RADIUS);
+        return TDK_ERR_INVALID;
+    }
+    GaussKernel g;
+    g.radius = radius;
+    for (int i = 0; i < 2 * radius + 1; i++) g.w[i] = kernel[i];
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((unsigned)((W + 63) / 64), (unsigned)((H + 3) / 4));
+    gauss_blur_axis_kernel<<<grid, TPB, 0, st>>>(image, tmp, (int)H, (int)W, 0, g);
+    gauss_blur_axis_kernel<<<grid, TPB, 0, st>>>(tmp, out, (int)H, (int)W, 1, g);
+    TDK_CUDA(cudaGetLastError());
+    return TDK_OK;
+}
+
+int tdk_resample_bilinear_dev(const double *image, int64_t H, int64_t W, double scale, double *out, int64_t h, int64_t w,
+                              void *stream)
+{
+    int rc = check_image("tdk_resample_bilinear_dev", H, W, image && out);
+    if (rc != TDK_OK) return rc;
+    if (!(scale > 0.) || h <= 0 || w <= 0 || h > 32767 || w > 32767) {
+        tdk_set_error("tdk_resample_bilinear_dev: bad scale or output size");
+        return TDK_ERR_INVALID;
+    }
+    dim3 grid((unsigned)((w + 63) / 64), (unsigned)((h + 3) / 4));
+    resample_bilinear_kernel<<<grid, TPB, 0, (cudaStream_t)stream>>>(image, (int)H, (int)W, out, (int)h, (int)w, scale);
     TDK_CUDA(cudaGetLastError());
     return TDK_OK;
 }

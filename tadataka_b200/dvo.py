@@ -14,8 +14,8 @@ reference's `Pose` objects.
 Deviations from the reference:
   * the least-squares step solves the 6x6 normal equations (minimum-norm, via lstsq) instead of
     running lstsq on the [N,6] system (tadataka/math.py:34-50): same minimiser, different rounding;
-  * the image pyramid (:139-148) uses `rescale` below (Gaussian pre-filter + bilinear), not
-    skimage.transform.rescale, which is not available here;
+  * the image pyramid (:139-148) uses `rescale` below (Gaussian pre-filter + bilinear; made on the
+    device by `rescale_device`), not skimage.transform.rescale, which is not available here;
 """
 import ctypes as C
 import warnings
@@ -260,6 +260,34 @@ def rescale(image, scale):
     return map_coordinates(smooth, [yy, xx], order=1, mode="reflect")
 
 
+def rescale_device(image, scale):
+    """`rescale` on the device (tdk_gaussian_blur_dev + tdk_resample_bilinear_dev): the same Gaussian
+    weights (scipy's: exp(-x^2 / 2 sigma^2) over |x| <= int(4 sigma + 0.5), normalised), the same
+    half-sample reflection and sampling grid; agrees with `rescale` to rounding (the sums run in
+    another order).  image: CUDA tensor [H,W] f64 -> CUDA tensor [round(H scale), round(W scale)]."""
+    image = _dev(image)
+    if scale == 1:
+        return image.clone()
+    H, W = image.shape
+    h, w = int(round(H * scale)), int(round(W * scale))
+    sigma = max(0.0, (1.0 / scale - 1.0) / 2.0)
+    smooth = image
+    if sigma > 0:
+        radius = int(4.0 * sigma + 0.5)
+        if radius > 32:
+            raise ValueError("scale too small for the device pyramid (Gaussian radius > 32)")
+        x = np.arange(-radius, radius + 1)
+        k = np.exp(-0.5 / (sigma * sigma) * x ** 2)
+        k = np.ascontiguousarray(k / k.sum())
+        tmp, smooth = torch.empty_like(image), torch.empty_like(image)
+        _lib.check(_lib.gaussian_blur_dev(device._ptr(image), H, W, _vp(k), radius, device._ptr(tmp),
+                                          device._ptr(smooth), device._stream()))
+    out = torch.empty((h, w), dtype=_F64, device=image.device)
+    _lib.check(_lib.resample_bilinear_dev(device._ptr(smooth), H, W, float(scale), device._ptr(out), h, w,
+                                          device._stream()))
+    return out
+
+
 class PoseChangeEstimator:
     """`PoseChangeEstimator(camera_params0, camera_params1, n_coarse_to_fine=5, max_iter=20,
     layer_size_ratio=1.5)`; call it with `(I0, D0, I1, weights=None, pose10=identity)`
@@ -274,14 +302,21 @@ class PoseChangeEstimator:
         self.layer_size_ratio = layer_size_ratio
 
     def __call__(self, I0, D0, I1, weights=None, pose10=None):
-        I0, D0, I1 = (np.asarray(a, dtype=np.float64) for a in (I0, D0, I1))
-        if not (I0.shape == D0.shape == I1.shape) or I0.ndim != 2:
+        """I0, D0, I1 (and a weight map): float64 [H,W] numpy arrays or CUDA tensors.  The images go to
+        the device once; every pyramid level is made there (`rescale_device`)."""
+        def up(a):
+            return _dev(a if isinstance(a, torch.Tensor) else np.asarray(a, dtype=np.float64))
+        if not (tuple(I0.shape) == tuple(D0.shape) == tuple(I1.shape)) or len(I0.shape) != 2:
             raise ValueError("I0, D0, I1 must be 2-D arrays of one shape")
+        I0, D0, I1 = up(I0), up(D0), up(I1)
+        wmap = None
+        if weights is not None and not isinstance(weights, str):
+            wmap = up(weights)
         T10 = np.eye(4) if pose10 is None else np.array(pose10, dtype=np.float64)
         for level in reversed(range(self.n_coarse_to_fine)):
             scale = 1 / pow(self.layer_size_ratio, level)      # level_to_scale, :42-43
-            W0 = rescale(weights, scale) if isinstance(weights, np.ndarray) else None
-            lv = _Level(self.cam0 * scale, self.cam1 * scale, rescale(I0, scale), rescale(D0, scale),
-                        rescale(I1, scale), W0)                # camera.resize, camera/model.py:69-74
-            T10 = _iterate(lv, T10, weights, self.max_iter)
+            W0 = rescale_device(wmap, scale) if wmap is not None else None
+            lv = _Level(self.cam0 * scale, self.cam1 * scale, rescale_device(I0, scale), rescale_device(D0, scale),
+                        rescale_device(I1, scale), W0)         # camera.resize, camera/model.py:69-74
+            T10 = _iterate(lv, T10, W0 if W0 is not None else weights, self.max_iter)
         return T10

@@ -173,3 +173,31 @@ def test_device_resident_loop_equals_the_host_loop_and_the_oracle(weights):
                                     dvo.HUBER_K if mode == 2 else 0.0, dvo._vp(level.cam0), dvo._vp(level.cam1),
                                     dvo._vp(T_dev), level.H, level.W, 0, 0, device._ptr(state), device._stream()))
     assert np.array_equal(state.cpu().numpy()[:16].reshape(4, 4), T_dev)
+
+
+def test_device_pyramid_is_the_numpy_pyramid():
+    """rescale_device (Gaussian pre-filter + bilinear resampling on the device) against `rescale`
+    (scipy gaussian_filter + map_coordinates): equal to rounding, on ragged and tiny images too; and
+    the coarse-to-fine estimator built on it against the same estimator fed a numpy-made pyramid."""
+    from tadataka_b200 import dvo
+    rng = np.random.default_rng(12)
+    for shape in [(97, 131), (480, 640), (7, 5), (33, 2)]:
+        img = rng.random(shape)
+        for level in range(5):
+            scale = 1 / pow(1.5, level)
+            if min(int(round(shape[0] * scale)), int(round(shape[1] * scale))) < 1:
+                continue
+            got = dvo.rescale_device(torch.from_numpy(img).cuda(), scale).cpu().numpy()
+            want = dvo.rescale(img, scale)
+            assert got.shape == want.shape
+            assert np.max(np.abs(got - want)) <= 1e-13, (shape, level)
+    cam, I0, D0, I1, _ = _pair(seed=9001, H=120, W=160, t=(4.0, -1.5, 2.0), rot=(0.01, -0.015, 0.008))
+    from rust_bindings.camera import CameraParameters
+    cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+    T = dvo.PoseChangeEstimator(cp, cp, n_coarse_to_fine=4, max_iter=20)(I0, D0, I1)
+    T_np = np.eye(4)
+    for level in reversed(range(4)):           # the same walk with the pyramid made by numpy
+        scale = 1 / pow(1.5, level)
+        lv = dvo._Level(cam * scale, cam * scale, dvo.rescale(I0, scale), dvo.rescale(D0, scale), dvo.rescale(I1, scale))
+        T_np = dvo._iterate(lv, T_np, None, 20)
+    assert np.max(np.abs(T - T_np)) <= 1e-8

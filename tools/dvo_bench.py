@@ -81,3 +81,25 @@ for name, T_w, in (("small motion", T_w1), ("larger motion", scene.pose(scene.ro
         t_dev = (time.perf_counter() - t0) / 10
         print(f"{name}, weights {w}: {len(tr)} iterations; host loop {t_host * 1e3:.2f} ms, device loop {t_dev * 1e3:.2f} ms, "
               f"max |dT| {np.max(np.abs(Th - Td)):.1e}")
+
+# the coarse-to-fine estimator on one VGA pair, 5 levels: pyramid made on the device against the numpy one
+from rust_bindings.camera import CameraParameters  # noqa: E402
+cp = CameraParameters((cam[0], cam[1]), (cam[2], cam[3]))
+est = dvo.PoseChangeEstimator(cp, cp, n_coarse_to_fine=5, max_iter=20)
+J1, _ = world.render(scene.pose(scene.rotation(0.012, -0.018, 0.009), (6.0, -2.5, 3.5)), cam, H, W)
+gI0, gD0, gJ1 = (torch.from_numpy(a).cuda() for a in (I0, D0, J1))
+for name, args in (("numpy images in", (I0, D0, J1)), ("CUDA tensors in", (gI0, gD0, gJ1))):
+    est(*args)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        T = est(*args)
+    t = (time.perf_counter() - t0) / 5
+    print(f"PoseChangeEstimator, 5 levels, {name}: {t * 1e3:.2f} ms per call")
+t0 = time.perf_counter()
+Tn = np.eye(4)
+for level in reversed(range(5)):
+    sc = 1 / pow(1.5, level)
+    lv = dvo._Level(cam * sc, cam * sc, dvo.rescale(I0, sc), dvo.rescale(D0, sc), dvo.rescale(J1, sc))
+    Tn = dvo._iterate(lv, Tn, None, 20)
+print(f"the same with the pyramid made by numpy / scipy on the host: {(time.perf_counter() - t0) * 1e3:.1f} ms; max |dT| {np.max(np.abs(T - Tn)):.1e}")
