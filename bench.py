@@ -586,6 +586,22 @@ def run_b200(args, rank, world, local_rank):
     if rank == 0 and world == 1 and not args.no_c4:
         import dropin_bench
         dropin = dropin_bench.run(refs=R, iters=20)
+        # the tracker on the other side of the loop: the 5-level direct pose-change
+        # estimator on one VGA pair, numpy images in, pyramid and Gauss-Newton loops on the device
+        from rust_bindings.camera import CameraParameters
+        from tadataka_b200 import dvo, scene as _scene
+        _w = _scene.World(_scene.SET_S, 9100)
+        _cam = _scene.CAM_VGA
+        _I0, _D0 = _w.render(_scene.pose(), _cam, H, W)
+        _I1, _ = _w.render(_scene.pose(_scene.rotation(0.012, -0.018, 0.009), (6.0, -2.5, 3.5)), _cam, H, W)
+        _cp = CameraParameters((_cam[0], _cam[1]), (_cam[2], _cam[3]))
+        _est = dvo.PoseChangeEstimator(_cp, _cp, n_coarse_to_fine=5, max_iter=20)
+        _est(_I0, _D0, _I1)
+        torch.cuda.synchronize()
+        _t0 = time.perf_counter()
+        for _ in range(5):
+            _est(_I0, _D0, _I1)
+        dropin["dvo_pose_change_5_levels_ms"] = 1e3 * (time.perf_counter() - _t0) / 5
 
     # ---- C5: the sharded run with the gather inside the clock (all ranks take part)
     c5 = None
